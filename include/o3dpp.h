@@ -1,0 +1,157 @@
+/*
+ * o3dpp.h — C ABI of libo3dpp_b200.so, the B200 (sm_100a) implementation of the
+ * open3dpypro point-cloud hot path.
+ *
+ * The reference (qinhy/Open3D-py-extension) has no FFI of its own: its hot path is
+ * four one-line delegations from open3dpypro/PointCloud.py into the open3d==0.19.0
+ * wheel.  Each entry point below names the reference call it replaces; the
+ * reference-side binding a maintainer would add is a ctypes stub.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative O3DPP_E_* code on failure;
+ *     o3dpp_last_error() returns the message of the last failure on this thread
+ *   - no exceptions and no torch/pybind types cross this boundary: plain pointers
+ *     and sizes only; the caller owns every buffer it passes
+ *   - host arrays are C-contiguous (n,3) row-major, float64 unless a dtype says
+ *     otherwise; *_dev variants take a CUDA device address (uintptr_t, e.g.
+ *     torch.Tensor.data_ptr()) instead of a host pointer
+ *   - one o3dpp_ctx belongs to one process and one GPU; it owns one CUDA stream
+ *     and all device memory of one cloud.  Calls on one ctx must not overlap.
+ *   - there is no CPU fallback: with no usable CUDA device o3dpp_create fails
+ */
+#ifndef O3DPP_H
+#define O3DPP_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define O3DPP_API __attribute__((visibility("default")))
+#else
+#define O3DPP_API
+#endif
+
+typedef struct o3dpp_ctx o3dpp_ctx;
+
+enum {
+    O3DPP_OK = 0,
+    O3DPP_E_CUDA = -1,        /* CUDA runtime error (message has the detail)            */
+    O3DPP_E_ARG = -2,         /* bad argument                                           */
+    O3DPP_E_VOXEL_SIZE = -3,  /* Open3D: "voxel_size <= 0."                             */
+    O3DPP_E_VOXEL_SMALL = -4, /* Open3D: "voxel_size is too small."                     */
+    O3DPP_E_RANSAC_N = -5,    /* Open3D: "ransac_n should be set to higher than or equal to 3." */
+    O3DPP_E_FEW_POINTS = -6,  /* Open3D: "There must be at least 'ransac_n' points."    */
+    O3DPP_E_PROB = -7,        /* Open3D: "Probability must be > 0 and <= 1.0"            */
+    O3DPP_E_STATE = -8,       /* call order (e.g. fetch before compute)                 */
+    O3DPP_E_UNSUPPORTED = -9  /* e.g. knn > O3DPP_MAX_KNN                               */
+};
+
+enum { O3DPP_F32 = 0, O3DPP_F64 = 1 };
+enum { O3DPP_SEARCH_KNN = 0, O3DPP_SEARCH_RADIUS = 1, O3DPP_SEARCH_HYBRID = 2 };
+enum { O3DPP_SAMPLER_PHILOX = 0, O3DPP_SAMPLER_MT19937 = 1, O3DPP_SAMPLER_GIVEN = 2 };
+enum { O3DPP_ATTR_POINTS = 0, O3DPP_ATTR_NORMALS = 1, O3DPP_ATTR_COLORS = 2 };
+
+#define O3DPP_MAX_KNN 128
+
+/* ---- library / context ---------------------------------------------------------- */
+O3DPP_API const char *o3dpp_last_error(void);
+O3DPP_API const char *o3dpp_version(void);
+O3DPP_API int o3dpp_device_count(int *count);
+O3DPP_API int o3dpp_create(int device, o3dpp_ctx **out);
+O3DPP_API int o3dpp_destroy(o3dpp_ctx *ctx);
+O3DPP_API int o3dpp_synchronize(o3dpp_ctx *ctx);
+/* CUDA stream of the context as an integer (cudaStream_t), for callers that time with
+ * events or enqueue their own work (torch.cuda.ExternalStream). */
+O3DPP_API int o3dpp_stream(o3dpp_ctx *ctx, uintptr_t *stream);
+/* Pinned host memory for the staging side of open3dpypro's Vector3dVector copies
+ * (PointCloud.py:94-107) and shmIO frames (shmIO.py:229-240). */
+O3DPP_API int o3dpp_host_alloc(void **ptr, uint64_t bytes);
+O3DPP_API int o3dpp_host_free(void *ptr);
+/* number of kernels this library has launched on the context since creation */
+O3DPP_API int o3dpp_launch_count(o3dpp_ctx *ctx, uint64_t *count);
+/* ms spent in the last call's stages, measured with CUDA events on the ctx stream.
+ * out[0..7]: operation specific, see each call. */
+O3DPP_API int o3dpp_last_timings(o3dpp_ctx *ctx, double *out8);
+
+/* ---- cloud state: replaces o3d.utility.Vector3dVector (PointCloud.py:94-107) ----- */
+/* attr = O3DPP_ATTR_*; uploading POINTS with a different n drops normals and colours */
+O3DPP_API int o3dpp_upload(o3dpp_ctx *ctx, int attr, const void *host, int64_t n, int dtype);
+O3DPP_API int o3dpp_upload_dev(o3dpp_ctx *ctx, int attr, uintptr_t dev, int64_t n, int dtype);
+/* replaces np.asarray(pcd.points / normals / colors) (PointCloud.py:119-126): float64 (n,3) */
+O3DPP_API int o3dpp_download(o3dpp_ctx *ctx, int attr, double *host);
+O3DPP_API int o3dpp_download_dev(o3dpp_ctx *ctx, int attr, uintptr_t dev, int dtype);
+O3DPP_API int o3dpp_size(o3dpp_ctx *ctx, int64_t *n);
+O3DPP_API int o3dpp_has(o3dpp_ctx *ctx, int attr, int *flag);
+O3DPP_API int o3dpp_drop(o3dpp_ctx *ctx, int attr);
+/* pcd.get_min_bound() / get_max_bound() (PointCloud.py:340): 3 + 3 float64 */
+O3DPP_API int o3dpp_bounds(o3dpp_ctx *ctx, double *min3, double *max3);
+
+/* ---- transform: replaces pcd.transform(T) (PointCloud.py:60-62) ------------------ */
+/* T = 16 float64 row-major.  points: (T[p,1]).xyz / w ; normals (if present): (T[n,0]).xyz */
+O3DPP_API int o3dpp_transform(o3dpp_ctx *ctx, const double *T16);
+
+/* ---- voxel_down_sample_and_trace: replaces pcd.voxel_down_sample_and_trace(
+ *      voxel_size, min_bound, max_bound, approximate_class=False) (PointCloud.py:338-341)
+ * Rows are in ascending (ix,iy,iz).  After o3dpp_voxel() the results stay on the device
+ * until the next o3dpp_voxel()/upload; fetch what is needed (NULL skips a field):
+ *   rep_asc   V  int32  idxmat.max(1) sorted ascending = PointCloud.py:341's mask order
+ *   rep       V  int32  largest original index per voxel, row order
+ *   count     V  int32  points per voxel
+ *   centroid  V*3 f64   mean position; normal V*3 f64 normalised normal sum (if normals);
+ *   color     V*3 f64   mean colour (if colours)
+ *   cubic_id  V*8 int32 largest original index per octant, -1 if empty
+ *   order     N  int32  original indices grouped by voxel row, ascending inside a row
+ *   seg       V+1 int64 row offsets into `order`
+ */
+O3DPP_API int o3dpp_voxel(o3dpp_ctx *ctx, double voxel_size, int64_t *V);
+O3DPP_API int o3dpp_voxel_fetch(o3dpp_ctx *ctx, int32_t *rep_asc, int32_t *rep, int32_t *count,
+                                double *centroid, double *normal, double *color,
+                                int32_t *cubic_id, int32_t *order, int64_t *seg);
+/* Replace the context's cloud by the selected original points (PointCloud.py:185-204 with
+ * idxmat.max(1)): points, normals, colours gathered in ascending original index. */
+O3DPP_API int o3dpp_voxel_select(o3dpp_ctx *ctx);
+
+/* ---- estimate_normals: replaces pcd.estimate_normals(param) (PointCloud.py:68-73),
+ *      fast_normal_computation = True.  mode = O3DPP_SEARCH_*; knn <= O3DPP_MAX_KNN.
+ * Normals are written into the context (ATTR_NORMALS); if the cloud already had normals
+ * the new ones are flipped to agree with them, as Open3D does.
+ * timings: [0] grid build (keys+sort+gather+cell boxes) [1] search+covariance+eigen   */
+O3DPP_API int o3dpp_estimate_normals(o3dpp_ctx *ctx, int mode, int knn, double radius);
+/* KDTreeFlann search of every point against the cloud (PointCloud.py:148-163 batched):
+ * idx (n*knn int32, -1 padded), d2 (n*knn f64, -1 padded, nullable), cnt (n int32, nullable);
+ * rows sorted by (d2, index). Host buffers. */
+O3DPP_API int o3dpp_knn(o3dpp_ctx *ctx, int mode, int knn, double radius,
+                        int32_t *idx, double *d2, int32_t *cnt);
+
+/* ---- segment_plane: replaces pcd.segment_plane(distance_threshold, ransac_n,
+ *      num_iterations, probability) (PointCloud.py:75-77)
+ * sampler PHILOX: counter-based Philox4x32-10 keyed by `seed`, generated on the device;
+ *         MT19937: std::mt19937(seed) replay of Open3D's RandomSampler;
+ *         GIVEN:   `samples` = num_iterations*ransac_n int64 host indices.
+ * plane4: refit plane of the final inliers.  n_inliers: size of the inlier list, fetched
+ * with o3dpp_fetch_inliers (ascending int32).  best_plane4 / best_iter (nullable): the
+ * winning pre-refit hypothesis.  counts/errs (nullable, num_iterations each): per
+ * hypothesis inlier count (-1 skipped by early exit, -2 degenerate) and distance sum.
+ * timings: [0] sampling+models [1] scoring [2] final pass+refit ; out8[7] = hypotheses scored */
+O3DPP_API int o3dpp_segment_plane(o3dpp_ctx *ctx, double distance_threshold, int ransac_n,
+                                  int num_iterations, double probability, int sampler,
+                                  uint64_t seed, const int64_t *samples, double *plane4,
+                                  int64_t *n_inliers, double *best_plane4, int32_t *best_iter,
+                                  int64_t *counts, double *errs);
+O3DPP_API int o3dpp_fetch_inliers(o3dpp_ctx *ctx, int32_t *out);
+/* the hypothesis sequence the last o3dpp_segment_plane used (H*ransac_n int64) */
+O3DPP_API int o3dpp_fetch_samples(o3dpp_ctx *ctx, int64_t *out);
+
+/* ---- selection: replaces PointCloudSelections._select_by_idx (PointCloud.py:185-204) */
+/* keep (invert=0) or drop (invert=1) the given original indices, ascending-index order */
+O3DPP_API int o3dpp_select(o3dpp_ctx *ctx, const int32_t *idx, int64_t m, int invert);
+/* same with the last segment_plane's inlier list, without a host round trip */
+O3DPP_API int o3dpp_select_inliers(o3dpp_ctx *ctx, int invert);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* O3DPP_H */

@@ -1,0 +1,155 @@
+// common.cuh — context, error plumbing and small device helpers shared by every kernel file.
+// Everything in csrc/ is compiled as ONE translation unit (o3dpp.cu) with -fmad=false so that
+// a*b+c is never contracted: the FP64 expressions below must round exactly like the CPU path
+// they replace (Open3D 0.19 built without -ffast-math).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <math.h>
+#include <string>
+#include <vector>
+#include "../../include/o3dpp.h"
+
+#define O3_SM_COUNT_FALLBACK 148
+
+static thread_local std::string g_last_error;
+
+static inline int set_err(int code, const std::string &msg)
+{
+    g_last_error = msg;
+    return code;
+}
+
+#define CU_TRY(expr)                                                                         \
+    do {                                                                                     \
+        cudaError_t _e = (expr);                                                             \
+        if (_e != cudaSuccess) {                                                             \
+            char _b[512];                                                                    \
+            snprintf(_b, sizeof _b, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),  \
+                     __FILE__, __LINE__);                                                    \
+            return set_err(O3DPP_E_CUDA, _b);                                                \
+        }                                                                                    \
+    } while (0)
+
+#define O3_TRY(expr)                  \
+    do {                              \
+        int _r = (expr);              \
+        if (_r != 0) return _r;       \
+    } while (0)
+
+// grow-only device buffer
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t bytes)
+    {
+        if (bytes <= cap) return 0;
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        size_t want = bytes + (bytes >> 3) + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) {
+            p = nullptr;
+            char b[256];
+            snprintf(b, sizeof b, "cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e));
+            return set_err(O3DPP_E_CUDA, b);
+        }
+        cap = want;
+        return 0;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T *as() const { return (T *)p; }
+};
+
+struct Attr3 {           // one (n,3) attribute stored as three planes (SoA), FP64
+    DevBuf buf;          // 3 * stride doubles
+    int64_t stride = 0;  // elements per plane (>= n, multiple of 32 so planes stay 256B aligned)
+    bool present = false;
+    double *x() const { return buf.as<double>(); }
+    double *y() const { return buf.as<double>() + stride; }
+    double *z() const { return buf.as<double>() + 2 * stride; }
+};
+
+static inline int64_t plane_stride(int64_t n) { return ((n + 31) / 32) * 32 + 32; }
+
+struct o3dpp_ctx {
+    int device = 0;
+    int sm_count = O3_SM_COUNT_FALLBACK;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    uint64_t launches = 0;
+    double timings[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+
+    int64_t n = 0;
+    Attr3 pts, nrm, col;
+
+    // staging for AoS <-> SoA conversion and small host round trips
+    DevBuf stage;
+    void *h_small = nullptr;  // pinned, 64 KiB
+    DevBuf d_small;           // 64 KiB device scratch for reductions / counters
+
+    // generic scratch (sort ping-pong, scan partials, ...)
+    DevBuf s_keys0, s_keys1, s_vals0, s_vals1, s_hist, s_scan, s_scan2, s_flags;
+
+    // voxel results (device resident until the next voxel()/upload)
+    bool vox_valid = false;
+    int64_t vox_V = 0, vox_n = 0;
+    DevBuf v_order, v_seg, v_oct, v_rep, v_rep_asc, v_count, v_centroid, v_normal, v_color, v_cubic;
+
+    // KNN grid (Morton-sorted cells, 32-point cell groups and their box hierarchy)
+    DevBuf g_sx, g_sy, g_sz, g_sidx, g_box, g_nbr, g_nd2, g_ncnt;
+
+    // RANSAC
+    DevBuf r_samples, r_planes, r_cnt, r_err, r_inl, r_part;
+    int64_t r_ninl = -1;
+    int r_H = 0, r_rn = 0;
+    std::vector<int64_t> r_samples_host;
+};
+
+#define LAUNCH(ctx, kernel, grid, block, smem, ...)                          \
+    do {                                                                     \
+        kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);     \
+        (ctx)->launches++;                                                   \
+    } while (0)
+
+static inline int check_launch(const char *what)
+{
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        char b[256];
+        snprintf(b, sizeof b, "kernel launch %s failed: %s", what, cudaGetErrorString(e));
+        return set_err(O3DPP_E_CUDA, b);
+    }
+    return 0;
+}
+
+static inline int grid_for(const o3dpp_ctx *c, int64_t work_items, int per_block, int waves_cap)
+{
+    int64_t g = (work_items + per_block - 1) / per_block;
+    int64_t cap = (int64_t)c->sm_count * waves_cap;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+// ---- device helpers ------------------------------------------------------------------
+#define FULL 0xffffffffu
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+
+__device__ __forceinline__ double shfl_d(double v, int src)
+{
+    return __shfl_sync(FULL, v, src);
+}
+__device__ __forceinline__ double shfl_xor_d(double v, int m) { return __shfl_xor_sync(FULL, v, m); }
+__device__ __forceinline__ double shfl_up_d(double v, int d) { return __shfl_up_sync(FULL, v, d); }
+__device__ __forceinline__ double shfl_down_d(double v, int d) { return __shfl_down_sync(FULL, v, d); }
+
+__device__ __forceinline__ double pos_inf() { return __longlong_as_double(0x7ff0000000000000LL); }
+
+// (dx*dx + dy*dy) + dz*dz, unfused: the nanoflann L2_Simple_Adaptor expression
+__device__ __forceinline__ double dist2_rn(double ax, double ay, double az, double bx, double by, double bz)
+{
+    double dx = __dsub_rn(ax, bx), dy = __dsub_rn(ay, by), dz = __dsub_rn(az, bz);
+    return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+}

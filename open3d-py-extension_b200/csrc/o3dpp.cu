@@ -1,0 +1,279 @@
+// o3dpp.cu — the C ABI declared in include/o3dpp.h.  Single translation unit:
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -fmad=false
+//        -Xcompiler -fPIC,-ffp-contract=off,-fvisibility=hidden -shared -o libo3dpp_b200.so o3dpp.cu
+// There is no CPU path in this library: every entry point needs a live CUDA context.
+#include "ransac.cuh"
+
+#define CTX_CHECK(c)                                                      \
+    do {                                                                  \
+        if (!(c)) return set_err(O3DPP_E_ARG, "null context");            \
+        cudaError_t _e = cudaSetDevice((c)->device);                      \
+        if (_e != cudaSuccess) return set_err(O3DPP_E_CUDA, cudaGetErrorString(_e)); \
+    } while (0)
+
+extern "C" {
+
+O3DPP_API const char *o3dpp_last_error(void) { return g_last_error.c_str(); }
+O3DPP_API const char *o3dpp_version(void) { return "o3dpp_b200 0.1 (sm_100a)"; }
+
+O3DPP_API int o3dpp_device_count(int *count)
+{
+    if (!count) return set_err(O3DPP_E_ARG, "null count");
+    *count = 0;
+    CU_TRY(cudaGetDeviceCount(count));
+    return 0;
+}
+
+O3DPP_API int o3dpp_create(int device, o3dpp_ctx **out)
+{
+    if (!out) return set_err(O3DPP_E_ARG, "null out");
+    *out = nullptr;
+    int cnt = 0;
+    CU_TRY(cudaGetDeviceCount(&cnt));
+    if (cnt <= 0) return set_err(O3DPP_E_CUDA, "no CUDA device: this library has no CPU fallback");
+    if (device < 0 || device >= cnt) return set_err(O3DPP_E_ARG, "device index out of range");
+    CU_TRY(cudaSetDevice(device));
+    o3dpp_ctx *c = new o3dpp_ctx();
+    c->device = device;
+    cudaDeviceProp prop;
+    CU_TRY(cudaGetDeviceProperties(&prop, device));
+    c->sm_count = prop.multiProcessorCount > 0 ? prop.multiProcessorCount : O3_SM_COUNT_FALLBACK;
+    CU_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 6; ++i) CU_TRY(cudaEventCreate(&c->ev[i]));
+    CU_TRY(cudaHostAlloc(&c->h_small, 64 * 1024, cudaHostAllocDefault));
+    O3_TRY(c->d_small.ensure(64 * 1024));
+    *out = c;
+    return 0;
+}
+
+O3DPP_API int o3dpp_destroy(o3dpp_ctx *c)
+{
+    if (!c) return 0;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    DevBuf *bufs[] = {&c->pts.buf, &c->nrm.buf, &c->col.buf, &c->stage, &c->d_small, &c->s_keys0, &c->s_keys1,
+                      &c->s_vals0, &c->s_vals1, &c->s_hist, &c->s_scan, &c->s_scan2, &c->s_flags, &c->v_order,
+                      &c->v_seg, &c->v_oct, &c->v_rep, &c->v_rep_asc, &c->v_count, &c->v_centroid, &c->v_normal,
+                      &c->v_color, &c->v_cubic, &c->g_sx, &c->g_sy, &c->g_sz, &c->g_sidx, &c->g_box, &c->g_nbr,
+                      &c->g_nd2, &c->g_ncnt, &c->r_samples, &c->r_planes, &c->r_cnt, &c->r_err, &c->r_inl, &c->r_part};
+    for (DevBuf *b : bufs) b->release();
+    if (c->h_small) cudaFreeHost(c->h_small);
+    for (int i = 0; i < 6; ++i) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return 0;
+}
+
+O3DPP_API int o3dpp_synchronize(o3dpp_ctx *c)
+{
+    CTX_CHECK(c);
+    CU_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+O3DPP_API int o3dpp_stream(o3dpp_ctx *c, uintptr_t *stream)
+{
+    if (!c || !stream) return set_err(O3DPP_E_ARG, "null argument");
+    *stream = (uintptr_t)c->stream;
+    return 0;
+}
+
+O3DPP_API int o3dpp_host_alloc(void **ptr, uint64_t bytes)
+{
+    if (!ptr) return set_err(O3DPP_E_ARG, "null ptr");
+    *ptr = nullptr;
+    CU_TRY(cudaHostAlloc(ptr, bytes ? bytes : 1, cudaHostAllocDefault));
+    return 0;
+}
+
+O3DPP_API int o3dpp_host_free(void *ptr)
+{
+    if (ptr) CU_TRY(cudaFreeHost(ptr));
+    return 0;
+}
+
+O3DPP_API int o3dpp_launch_count(o3dpp_ctx *c, uint64_t *count)
+{
+    if (!c || !count) return set_err(O3DPP_E_ARG, "null argument");
+    *count = c->launches;
+    return 0;
+}
+
+O3DPP_API int o3dpp_last_timings(o3dpp_ctx *c, double *out8)
+{
+    if (!c || !out8) return set_err(O3DPP_E_ARG, "null argument");
+    memcpy(out8, c->timings, sizeof c->timings);
+    return 0;
+}
+
+O3DPP_API int o3dpp_upload(o3dpp_ctx *c, int attr, const void *host, int64_t n, int dtype)
+{
+    CTX_CHECK(c);
+    O3_TRY(upload_impl(c, attr, host, false, n, dtype));
+    // the staging buffer is reused by the next call: finish the copy before returning
+    CU_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+O3DPP_API int o3dpp_upload_dev(o3dpp_ctx *c, int attr, uintptr_t dev, int64_t n, int dtype)
+{
+    CTX_CHECK(c);
+    O3_TRY(upload_impl(c, attr, (const void *)dev, true, n, dtype));
+    CU_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+O3DPP_API int o3dpp_download(o3dpp_ctx *c, int attr, double *host)
+{
+    CTX_CHECK(c);
+    return download_impl(c, attr, host, false, O3DPP_F64);
+}
+
+O3DPP_API int o3dpp_download_dev(o3dpp_ctx *c, int attr, uintptr_t dev, int dtype)
+{
+    CTX_CHECK(c);
+    O3_TRY(download_impl(c, attr, (void *)dev, true, dtype));
+    CU_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+O3DPP_API int o3dpp_size(o3dpp_ctx *c, int64_t *n)
+{
+    if (!c || !n) return set_err(O3DPP_E_ARG, "null argument");
+    *n = c->n;
+    return 0;
+}
+
+O3DPP_API int o3dpp_has(o3dpp_ctx *c, int attr, int *flag)
+{
+    if (!c || !flag) return set_err(O3DPP_E_ARG, "null argument");
+    Attr3 *a = attr_of(c, attr);
+    if (!a) return set_err(O3DPP_E_ARG, "unknown attribute");
+    *flag = a->present ? 1 : 0;
+    return 0;
+}
+
+O3DPP_API int o3dpp_drop(o3dpp_ctx *c, int attr)
+{
+    if (!c) return set_err(O3DPP_E_ARG, "null context");
+    if (attr == O3DPP_ATTR_NORMALS) c->nrm.present = false;
+    else if (attr == O3DPP_ATTR_COLORS) c->col.present = false;
+    else if (attr == O3DPP_ATTR_POINTS) { c->n = 0; c->pts.present = false; c->nrm.present = false; c->col.present = false; invalidate_derived(c); }
+    else return set_err(O3DPP_E_ARG, "unknown attribute");
+    return 0;
+}
+
+O3DPP_API int o3dpp_bounds(o3dpp_ctx *c, double *min3, double *max3)
+{
+    CTX_CHECK(c);
+    double mn[3], mx[3];
+    O3_TRY(bounds_impl(c, mn, mx));
+    if (min3) memcpy(min3, mn, sizeof mn);
+    if (max3) memcpy(max3, mx, sizeof mx);
+    return 0;
+}
+
+O3DPP_API int o3dpp_transform(o3dpp_ctx *c, const double *T16)
+{
+    CTX_CHECK(c);
+    O3_TRY(transform_impl(c, T16));
+    CU_TRY(cudaStreamSynchronize(c->stream));
+    if (c->n > 0) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]);
+        c->timings[0] = ms;
+    }
+    return 0;
+}
+
+O3DPP_API int o3dpp_voxel(o3dpp_ctx *c, double voxel_size, int64_t *V)
+{
+    CTX_CHECK(c);
+    return voxel_impl(c, voxel_size, V);
+}
+
+O3DPP_API int o3dpp_voxel_fetch(o3dpp_ctx *c, int32_t *rep_asc, int32_t *rep, int32_t *count, double *centroid,
+                                double *normal, double *color, int32_t *cubic_id, int32_t *order, int64_t *seg)
+{
+    CTX_CHECK(c);
+    return voxel_fetch_impl(c, rep_asc, rep, count, centroid, normal, color, cubic_id, order, seg);
+}
+
+O3DPP_API int o3dpp_voxel_select(o3dpp_ctx *c)
+{
+    CTX_CHECK(c);
+    return voxel_select_impl(c);
+}
+
+O3DPP_API int o3dpp_estimate_normals(o3dpp_ctx *c, int mode, int knn, double radius)
+{
+    CTX_CHECK(c);
+    return search_impl(c, mode, knn, radius, true, nullptr, nullptr, nullptr);
+}
+
+O3DPP_API int o3dpp_knn(o3dpp_ctx *c, int mode, int knn, double radius, int32_t *idx, double *d2, int32_t *cnt)
+{
+    CTX_CHECK(c);
+    if (!idx) return set_err(O3DPP_E_ARG, "idx is required");
+    return search_impl(c, mode, knn, radius, false, idx, d2, cnt);
+}
+
+O3DPP_API int o3dpp_segment_plane(o3dpp_ctx *c, double distance_threshold, int ransac_n, int num_iterations,
+                                  double probability, int sampler, uint64_t seed, const int64_t *samples,
+                                  double *plane4, int64_t *n_inliers, double *best_plane4, int32_t *best_iter,
+                                  int64_t *counts, double *errs)
+{
+    CTX_CHECK(c);
+    return segment_plane_impl(c, distance_threshold, ransac_n, num_iterations, probability, sampler, seed, samples,
+                              plane4, n_inliers, best_plane4, best_iter, counts, errs);
+}
+
+O3DPP_API int o3dpp_fetch_inliers(o3dpp_ctx *c, int32_t *out)
+{
+    CTX_CHECK(c);
+    if (c->r_ninl < 0) return set_err(O3DPP_E_STATE, "o3dpp_segment_plane has not been run on the current cloud");
+    O3_TRY(d2h(c, out, c->r_inl.p, (size_t)c->r_ninl * 4));
+    CU_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+O3DPP_API int o3dpp_fetch_samples(o3dpp_ctx *c, int64_t *out)
+{
+    if (!c || !out) return set_err(O3DPP_E_ARG, "null argument");
+    if (c->r_samples_host.empty() && c->r_H > 0) return set_err(O3DPP_E_STATE, "no samples");
+    memcpy(out, c->r_samples_host.data(), c->r_samples_host.size() * sizeof(int64_t));
+    return 0;
+}
+
+O3DPP_API int o3dpp_select(o3dpp_ctx *c, const int32_t *idx, int64_t m, int invert)
+{
+    CTX_CHECK(c);
+    if (m < 0 || (m > 0 && !idx)) return set_err(O3DPP_E_ARG, "bad index list");
+    DevBuf d;
+    O3_TRY(d.ensure((size_t)(m + 16) * 4));
+    int rc = 0;
+    if (m > 0 && cudaMemcpyAsync(d.p, idx, (size_t)m * 4, cudaMemcpyHostToDevice, c->stream) != cudaSuccess)
+        rc = set_err(O3DPP_E_CUDA, "copy failed");
+    if (!rc) rc = select_impl(c, d.as<int32_t>(), m, invert);
+    cudaStreamSynchronize(c->stream);
+    d.release();
+    return rc;
+}
+
+O3DPP_API int o3dpp_select_inliers(o3dpp_ctx *c, int invert)
+{
+    CTX_CHECK(c);
+    if (c->r_ninl < 0) return set_err(O3DPP_E_STATE, "o3dpp_segment_plane has not been run on the current cloud");
+    DevBuf d;
+    int64_t m = c->r_ninl;
+    O3_TRY(d.ensure((size_t)(m + 16) * 4));
+    int rc = 0;
+    if (m > 0 && cudaMemcpyAsync(d.p, c->r_inl.p, (size_t)m * 4, cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess)
+        rc = set_err(O3DPP_E_CUDA, "copy failed");
+    if (!rc) rc = select_impl(c, d.as<int32_t>(), m, invert);
+    cudaStreamSynchronize(c->stream);
+    d.release();
+    return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,281 @@
+"""ctypes binding of libo3dpp_b200.so (include/o3dpp.h).
+
+This is the only place the package touches native code.  There is no CPU fallback: if the
+library is missing it is built with nvcc; if it cannot be loaded, or no CUDA device is usable,
+the error is raised to the caller.
+"""
+import ctypes as C
+import os
+import threading
+
+import numpy as np
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_PKG)
+LIB_PATH = os.path.join(_ROOT, "libo3dpp_b200.so")
+
+ATTR_POINTS, ATTR_NORMALS, ATTR_COLORS = 0, 1, 2
+SEARCH_KNN, SEARCH_RADIUS, SEARCH_HYBRID = 0, 1, 2
+SAMPLER_PHILOX, SAMPLER_MT19937, SAMPLER_GIVEN = 0, 1, 2
+F32, F64 = 0, 1
+MAX_KNN = 128
+
+# every symbol include/o3dpp.h declares (tests check the library exports all of them)
+SYMBOLS = [
+    "o3dpp_last_error", "o3dpp_version", "o3dpp_device_count", "o3dpp_create", "o3dpp_destroy",
+    "o3dpp_synchronize", "o3dpp_stream", "o3dpp_host_alloc", "o3dpp_host_free", "o3dpp_launch_count",
+    "o3dpp_last_timings", "o3dpp_upload", "o3dpp_upload_dev", "o3dpp_download", "o3dpp_download_dev",
+    "o3dpp_size", "o3dpp_has", "o3dpp_drop", "o3dpp_bounds", "o3dpp_transform", "o3dpp_voxel",
+    "o3dpp_voxel_fetch", "o3dpp_voxel_select", "o3dpp_estimate_normals", "o3dpp_knn",
+    "o3dpp_segment_plane", "o3dpp_fetch_inliers", "o3dpp_fetch_samples", "o3dpp_select",
+    "o3dpp_select_inliers",
+]
+
+_lib = None
+_lock = threading.Lock()
+
+
+class O3dppError(RuntimeError):
+    """Raised for every non-zero status of the C ABI; `.code` is the O3DPP_E_* value.
+
+    Open3D raises RuntimeError for the same conditions (bad voxel_size, ransac_n < 3, ...), so
+    code written against the reference keeps catching it."""
+
+    def __init__(self, code, msg):
+        super().__init__(msg)
+        self.code = code
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        with _lock:
+            if _lib is None:
+                if not os.path.exists(LIB_PATH):
+                    import importlib.util
+                    spec = importlib.util.spec_from_file_location("_o3dpp_build", os.path.join(_ROOT, "build.py"))
+                    mod = importlib.util.module_from_spec(spec)
+                    spec.loader.exec_module(mod)
+                    mod.build()
+                L = C.CDLL(LIB_PATH)
+                L.o3dpp_last_error.restype = C.c_char_p
+                L.o3dpp_version.restype = C.c_char_p
+                _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        msg = lib().o3dpp_last_error()
+        raise O3dppError(rc, (msg or b"").decode("utf-8", "replace") or f"o3dpp error {rc}")
+
+
+def device_count():
+    n = C.c_int(0)
+    _check(lib().o3dpp_device_count(C.byref(n)))
+    return n.value
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class PinnedArray:
+    """numpy array over cudaHostAlloc memory (page-locked, so H2D/D2H run at full PCIe speed)."""
+
+    def __init__(self, shape, dtype=np.float64):
+        self.shape = tuple(int(s) for s in np.atleast_1d(shape))
+        self.dtype = np.dtype(dtype)
+        nbytes = int(np.prod(self.shape)) * self.dtype.itemsize
+        self._ptr = C.c_void_p()
+        _check(lib().o3dpp_host_alloc(C.byref(self._ptr), C.c_uint64(max(nbytes, 1))))
+        buf = (C.c_char * max(nbytes, 1)).from_address(self._ptr.value)
+        self.array = np.frombuffer(buf, dtype=self.dtype, count=int(np.prod(self.shape))).reshape(self.shape)
+
+    def free(self):
+        if self._ptr is not None and self._ptr.value:
+            self.array = None
+            try:
+                lib().o3dpp_host_free(self._ptr)
+            except Exception:
+                pass
+            self._ptr = None
+
+    def __del__(self):
+        self.free()
+
+
+class Context:
+    """One device-resident cloud on one GPU (o3dpp_ctx).  Created lazily, per process."""
+
+    def __init__(self, device=0):
+        self._h = C.c_void_p()
+        self.device = device
+        self._pid = os.getpid()
+        _check(lib().o3dpp_create(C.c_int(device), C.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value and self._pid == os.getpid():
+            lib().o3dpp_destroy(self._h)
+        self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- state
+    def upload(self, attr, arr):
+        a = np.asarray(arr)
+        if a.dtype == np.float32:
+            dt = F32
+        else:
+            dt = F64
+            if a.dtype != np.float64:
+                a = a.astype(np.float64)
+        if a.ndim != 2 or a.shape[1] != 3:
+            raise ValueError("expected an (n,3) array")
+        a = np.ascontiguousarray(a)
+        _check(lib().o3dpp_upload(self._h, C.c_int(attr), _ptr(a), C.c_int64(a.shape[0]), C.c_int(dt)))
+
+    def upload_dev(self, attr, dev_ptr, n, dtype=F64):
+        _check(lib().o3dpp_upload_dev(self._h, C.c_int(attr), C.c_size_t(dev_ptr), C.c_int64(n), C.c_int(dtype)))
+
+    def download(self, attr, out=None):
+        n = self.size()
+        if out is None:
+            out = np.empty((n, 3), np.float64)
+        assert out.dtype == np.float64 and out.flags.c_contiguous and out.shape == (n, 3)
+        if n:
+            _check(lib().o3dpp_download(self._h, C.c_int(attr), _ptr(out)))
+        return out
+
+    def download_dev(self, attr, dev_ptr, dtype=F64):
+        _check(lib().o3dpp_download_dev(self._h, C.c_int(attr), C.c_size_t(dev_ptr), C.c_int(dtype)))
+
+    def size(self):
+        n = C.c_int64(0)
+        _check(lib().o3dpp_size(self._h, C.byref(n)))
+        return n.value
+
+    def has(self, attr):
+        f = C.c_int(0)
+        _check(lib().o3dpp_has(self._h, C.c_int(attr), C.byref(f)))
+        return bool(f.value)
+
+    def drop(self, attr):
+        _check(lib().o3dpp_drop(self._h, C.c_int(attr)))
+
+    def synchronize(self):
+        _check(lib().o3dpp_synchronize(self._h))
+
+    def stream(self):
+        s = C.c_size_t(0)
+        _check(lib().o3dpp_stream(self._h, C.byref(s)))
+        return s.value
+
+    def launch_count(self):
+        n = C.c_uint64(0)
+        _check(lib().o3dpp_launch_count(self._h, C.byref(n)))
+        return n.value
+
+    def timings(self):
+        t = np.zeros(8, np.float64)
+        _check(lib().o3dpp_last_timings(self._h, _ptr(t)))
+        return t
+
+    def bounds(self):
+        mn, mx = np.zeros(3), np.zeros(3)
+        _check(lib().o3dpp_bounds(self._h, _ptr(mn), _ptr(mx)))
+        return mn, mx
+
+    # ---- operations
+    def transform(self, T):
+        T = np.ascontiguousarray(np.asarray(T, dtype=np.float64).reshape(16))
+        _check(lib().o3dpp_transform(self._h, _ptr(T)))
+
+    def voxel(self, voxel_size):
+        V = C.c_int64(0)
+        _check(lib().o3dpp_voxel(self._h, C.c_double(voxel_size), C.byref(V)))
+        return V.value
+
+    def voxel_fetch(self, V, n, fields=("rep_asc",)):
+        """fields: any of rep_asc, rep, count, centroid, normal, color, cubic_id, order, seg"""
+        spec = {
+            "rep_asc": ((V,), np.int32), "rep": ((V,), np.int32), "count": ((V,), np.int32),
+            "centroid": ((V, 3), np.float64), "normal": ((V, 3), np.float64), "color": ((V, 3), np.float64),
+            "cubic_id": ((V, 8), np.int32), "order": ((n,), np.int32), "seg": ((V + 1,), np.int64),
+        }
+        out = {k: np.empty(spec[k][0], spec[k][1]) for k in fields}
+        args = [_ptr(out.get(k)) for k in ("rep_asc", "rep", "count", "centroid", "normal", "color", "cubic_id", "order", "seg")]
+        _check(lib().o3dpp_voxel_fetch(self._h, *args))
+        return out
+
+    def voxel_select(self):
+        _check(lib().o3dpp_voxel_select(self._h))
+
+    def estimate_normals(self, mode, knn, radius):
+        _check(lib().o3dpp_estimate_normals(self._h, C.c_int(mode), C.c_int(knn), C.c_double(radius)))
+
+    def knn(self, mode, knn, radius=0.0, want_d2=True):
+        n = self.size()
+        idx = np.empty((n, knn), np.int32)
+        d2 = np.empty((n, knn), np.float64) if want_d2 else None
+        cnt = np.empty(n, np.int32)
+        _check(lib().o3dpp_knn(self._h, C.c_int(mode), C.c_int(knn), C.c_double(radius), _ptr(idx), _ptr(d2), _ptr(cnt)))
+        return idx, d2, cnt
+
+    def segment_plane(self, distance_threshold, ransac_n, num_iterations, probability=0.99999999,
+                      sampler=SAMPLER_PHILOX, seed=0, samples=None, debug=False, fetch_inliers=True):
+        H = int(num_iterations)
+        plane = np.zeros(4)
+        best = np.zeros(4)
+        m = C.c_int64(0)
+        bi = C.c_int32(-1)
+        counts = np.empty(max(H, 1), np.int64) if debug else None
+        errs = np.empty(max(H, 1), np.float64) if debug else None
+        s = None
+        if samples is not None:
+            s = np.ascontiguousarray(np.asarray(samples, dtype=np.int64).reshape(-1))
+            if s.size != H * int(ransac_n):
+                raise ValueError("samples must hold num_iterations*ransac_n indices")
+            sampler = SAMPLER_GIVEN
+        _check(lib().o3dpp_segment_plane(self._h, C.c_double(distance_threshold), C.c_int(ransac_n), C.c_int(H),
+                                         C.c_double(probability), C.c_int(sampler), C.c_uint64(seed), _ptr(s),
+                                         _ptr(plane), C.byref(m), _ptr(best), C.byref(bi), _ptr(counts), _ptr(errs)))
+        inl = None
+        if fetch_inliers:
+            inl = np.empty(m.value, np.int32)
+            if m.value:
+                _check(lib().o3dpp_fetch_inliers(self._h, _ptr(inl)))
+        if debug:
+            return plane, inl, dict(best_plane=best, best_iter=bi.value, counts=counts[:H], errs=errs[:H],
+                                    n_inliers=m.value)
+        return plane, inl
+
+    def fetch_samples(self, H, ransac_n):
+        out = np.empty((H, ransac_n), np.int64)
+        if H:
+            _check(lib().o3dpp_fetch_samples(self._h, _ptr(out)))
+        return out
+
+    def select(self, idx, invert=False):
+        idx = np.ascontiguousarray(np.asarray(idx, dtype=np.int32).reshape(-1))
+        _check(lib().o3dpp_select(self._h, _ptr(idx), C.c_int64(idx.size), C.c_int(int(invert))))
+
+    def select_inliers(self, invert=False):
+        _check(lib().o3dpp_select_inliers(self._h, C.c_int(int(invert))))
+
+
+_contexts = {}
+
+
+def context(device=0):
+    """Process-wide shared context per device, re-created after fork (CUDA state does not survive it)."""
+    key = (os.getpid(), int(device))
+    ctx = _contexts.get(key)
+    if ctx is None:
+        ctx = Context(device)
+        _contexts[key] = ctx
+    return ctx
