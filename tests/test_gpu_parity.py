@@ -179,15 +179,32 @@ def _check_normals(ctx, orc, pts, mode, k, radius, old=None, exact=True):
         ctx.drop(nat.ATTR_NORMALS)
     ctx.estimate_normals(mode, k, radius)
     got = ctx.download(nat.ATTR_NORMALS)
-    ref = orc.estimate_normals(pts, mode={0: "knn", 1: "radius", 2: "hybrid"}[mode], k=k, radius=radius, old_normals=old)
+    ref, cov = orc.estimate_normals(pts, mode={0: "knn", 1: "radius", 2: "hybrid"}[mode], k=k, radius=radius,
+                                    old_normals=old, want_cov=True)
+    # conditioning of every 3x3 problem: the closed form loses the direction when the two smallest
+    # eigenvalues coincide (collinear neighbourhoods), so the angle bar applies where the gap is real
+    Cm = np.empty((len(pts), 3, 3))
+    Cm[:, 0, 0], Cm[:, 0, 1], Cm[:, 0, 2] = cov[:, 0], cov[:, 1], cov[:, 2]
+    Cm[:, 1, 0], Cm[:, 1, 1], Cm[:, 1, 2] = cov[:, 1], cov[:, 3], cov[:, 4]
+    Cm[:, 2, 0], Cm[:, 2, 1], Cm[:, 2, 2] = cov[:, 2], cov[:, 4], cov[:, 5]
+    lam = np.linalg.eigvalsh(Cm)
+    scale = np.maximum(np.abs(lam).max(1), 1e-300)
+    well = (lam[:, 1] - lam[:, 0]) / scale > 1e-6
     ang = _angle(got, ref)
-    assert np.nanmax(ang) < 1e-4, f"max angle {np.nanmax(ang)}"
+    assert np.isfinite(got).all()
+    assert np.abs(np.linalg.norm(got, axis=1) - 1.0).max() < 1e-9
+    assert ang[well].max(initial=0.0) < 1e-4, f"max angle {ang[well].max()}"
+    # everywhere: the returned direction is as good a minimiser of n^T C n as the oracle's
+    ray_got = np.einsum("ni,nij,nj->n", got, Cm, got)
+    ray_ref = np.einsum("ni,nij,nj->n", ref, Cm, ref)
+    assert ((ray_got - ray_ref) / scale).max() < 1e-9
     if old is not None:  # sign must follow the old normals exactly as the oracle does
-        assert (np.einsum("ij,ij->i", got, ref) > 0).all()
+        assert (np.einsum("ij,ij->i", got, ref)[well] > 0).all()
     if exact:
         # same neighbour order, same cumulant order, same solver: only libm acos/cos may differ
-        assert np.abs(got - ref).max() < 1e-9 or np.abs(np.abs(got) - np.abs(ref)).max() < 1e-9
+        assert np.abs(got[well] - ref[well]).max(initial=0.0) < 1e-7
     ctx.drop(nat.ATTR_NORMALS)
+    return well.mean()
 
 
 def test_normals_bunny_knn(ctx, orc, bunny):
