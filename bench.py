@@ -1,0 +1,270 @@
+#!/usr/bin/env python
+"""Benchmark of the point-cloud hot path (BASELINE.json metric):
+    Mpoints/s of estimate_normals + segment_plane on a 10 M-point synthetic LiDAR-like scan.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--points P]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One step = one pass of the hot path over one scan: voxel_down_sample(0.1) (timed, reported under
+`stages_ms`, not part of the metric), then estimate_normals(KNN k=30) and segment_plane(0.05, 3,
+1000) on the full scan.  `value` = points / (t_normals + t_segment), inputs resident in HBM.
+`e2e` = the same two calls through the C ABI with page-locked HOST buffers: H2D of the float64
+(N,3) points, D2H of the float64 normals, the inlier list and the plane inside the timed region.
+At N > 1 every rank owns its own scan (frame/scan sharding, no data-path collective): weak scaling.
+`--impl reference` times the CPU oracle (a restatement of Open3D 0.19's algorithms, the reference's
+CPU path; the Open3D wheel itself is not installable here) on the host cores.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "open3d-py-extension_b200"))
+
+import numpy as np  # noqa: E402
+
+METRIC = "Mpoints/s estimate_normals+segment_plane @10M pts"
+VOXEL, KNN, THR, RANSAC_N, ITERS = 0.1, 30, 0.05, 3, 1000
+ALGO_BYTES_PER_POINT_KNN = 384.0   # N*(12 + 12k + 12) at k = 30
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, line in self.rows:
+            f = [v.strip() for v in line.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                mx = float(f[1])
+                if t0 - 0.05 <= ts <= t1 + 0.15:
+                    sm.append(float(f[0]))
+                    for nme, v in zip(names, f[2:6]):
+                        if v.lower().startswith("active"):
+                            reasons.add(nme)
+            except ValueError:
+                continue
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def oracle_pass(pts, threads):
+    """one CPU pass of the metric's two calls on `pts`; returns seconds"""
+    from oracle import orc
+    t = time.perf_counter()
+    orc.estimate_normals(pts, "knn", KNN, nthreads=threads)
+    samples = orc.sample_philox(1, len(pts), RANSAC_N, ITERS)
+    orc.segment_plane(pts, THR, RANSAC_N, ITERS, samples, nthreads=threads)
+    return time.perf_counter() - t
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    from oracle import orc
+    from open3dpypro.synthetic import lidar_like, SEED_C3
+    threads = os.cpu_count() or 1
+    n = min(args.points, args.ref_points)
+    pts = lidar_like(n, SEED_C3)
+    for _ in range(min(args.warmup, 1)):
+        oracle_pass(pts[: max(n // 10, 1000)], threads)
+    ts = [oracle_pass(pts, threads) for _ in range(args.steps)]
+    ms = 1e3 * sum(ts) / len(ts)
+    val = n / (ms * 1e-3) / 1e6
+    sample = f"{n}-point scan from the same generator (seed {SEED_C3}), KNN k={KNN} normals + segment_plane({THR},{RANSAC_N},{ITERS}), OpenMP on all host threads"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "Mpoints/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "C3: synthetic 10M-point scan, estimate_normals(k=30)+segment_plane(0.05,3,1000)",
+                   "points_per_step": n, "note": "CPU oracle = C restatement of Open3D 0.19 (wheel unavailable on this box)"},
+        "cpu_baseline": {"value": val, "unit": "Mpoints/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "Mpoints/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--points", type=int, default=10_000_000)
+    ap.add_argument("--ref-points", type=int, default=10_000_000, help="bounded CPU sample size")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    from open3dpypro import _native as nat
+    from open3dpypro.synthetic import lidar_like, SEED_C3
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    N = args.points
+    pts = lidar_like(N, SEED_C3 + rank)          # every rank owns its own scan
+    ctx = nat.Context(local)
+    stream = torch.cuda.ExternalStream(ctx.stream(), device=local)
+    hin = nat.PinnedArray((N, 3), np.float64)
+    hin.array[...] = pts
+    hout = nat.PinnedArray((N, 3), np.float64)
+    ctx.upload(nat.ATTR_POINTS, hin.array)
+
+    def device_step(stages):
+        ctx.drop(nat.ATTR_NORMALS)
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        e[0].record(stream)
+        V = ctx.voxel(VOXEL)
+        e[1].record(stream)
+        ctx.estimate_normals(nat.SEARCH_KNN, KNN, 0.0)
+        tk = ctx.timings()
+        e[2].record(stream)
+        plane, _ = ctx.segment_plane(THR, RANSAC_N, ITERS, seed=1, fetch_inliers=False)
+        ts = ctx.timings()
+        e[3].record(stream)
+        e[3].synchronize()
+        stages.append({"voxel": e[0].elapsed_time(e[1]), "normals": e[1].elapsed_time(e[2]),
+                       "segment": e[2].elapsed_time(e[3]), "grid_build": tk[0], "knn_kernel": tk[1],
+                       "ransac_score": ts[1], "ransac_scored": ts[7], "V": V})
+        return plane
+
+    def e2e_step():
+        ctx.upload(nat.ATTR_POINTS, hin.array)          # H2D 24 B/point from page-locked memory
+        ctx.drop(nat.ATTR_NORMALS)
+        ctx.estimate_normals(nat.SEARCH_KNN, KNN, 0.0)
+        plane, inl = ctx.segment_plane(THR, RANSAC_N, ITERS, seed=1)   # D2H inliers + plane
+        ctx.download(nat.ATTR_NORMALS, hout.array)       # D2H 24 B/point
+        return plane, inl
+
+    scratch = []
+    for _ in range(args.warmup):
+        device_step(scratch)
+    barrier()
+    sampler = ClockSampler(local)
+    l0 = ctx.launch_count()
+    stages = []
+    wall0 = time.time()
+    for _ in range(args.steps):
+        device_step(stages)
+    barrier()
+    wall1 = time.time()
+    launches = ctx.launch_count() - l0
+    clocks = sampler.stop(wall0, wall1)
+    t_metric = sum(s["normals"] + s["segment"] for s in stages) / len(stages)      # ms
+    t_step = sum(s["voxel"] + s["normals"] + s["segment"] for s in stages) / len(stages)
+
+    for _ in range(max(1, min(args.warmup, 2))):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        plane, inl = e2e_step()
+    barrier()
+    t_e2e = (time.perf_counter() - t0) * 1e3 / args.steps
+    n_inl = int(len(inl))
+
+    tm = torch.tensor([t_metric, t_step, t_e2e], dtype=torch.float64, device=f"cuda:{local}")
+    if dist is not None:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    t_metric, t_step, t_e2e = [float(v) for v in tm.tolist()]
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        knn_ms = sum(s["knn_kernel"] for s in stages) / len(stages)
+        achieved = ALGO_BYTES_PER_POINT_KNN * N / (knn_ms * 1e-3) / 1e9
+        med = {k: statistics.median(s[k] for s in stages) for k in stages[0]}
+        out = {
+            "metric": METRIC, "value": world * N / (t_metric * 1e-3) / 1e6, "unit": "Mpoints/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_metric, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "C3: synthetic 10M-point scan, estimate_normals(k=30)+segment_plane(0.05,3,1000)"
+                                   " (voxel_down_sample(0.1) timed beside it)",
+                       "points_per_gpu": N, "sharding": "one scan per GPU, no data-path collective",
+                       "l2": "inputs (240 MB FP64 planes per scan) exceed the 126 MB L2",
+                       "timing": "CUDA events on the library stream; max over ranks"},
+            "stages_ms": med, "chain_ms_per_step": t_step,
+            "e2e": {"value": world * N / (t_e2e * 1e-3) / 1e6, "unit": "Mpoints/s", "ms_per_step": t_e2e,
+                    "h2d_bytes_per_step": 24 * N, "d2h_bytes_per_step": 24 * N + 4 * n_inl + 32},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "knn_normals_kernel", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": ALGO_BYTES_PER_POINT_KNN * N, "kernel_ms": knn_ms},
+            "clocks": clocks,
+        }
+        if not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            n = min(N, args.ref_points)
+            sec = oracle_pass(lidar_like(n, SEED_C3), threads)
+            out["cpu_baseline"] = {"value": n / sec / 1e6, "unit": "Mpoints/s", "cores": threads, "kind": "port",
+                                   "sample": f"one pass over a {n}-point scan of the same generator ({sec:.1f} s), "
+                                             f"C oracle (Open3D 0.19 restatement), OpenMP on all host threads"}
+        traffic = os.path.join(ROOT, "profiles", "knn_traffic.json")
+        if os.path.exists(traffic):
+            try:
+                out["roofline"]["traffic"] = json.load(open(traffic)).get("dram_bytes_per_launch")
+            except Exception:
+                pass
+        print(json.dumps(out))
+    hin.free()
+    hout.free()
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -75,6 +75,9 @@ O3DPP_API int o3dpp_launch_count(o3dpp_ctx *ctx, uint64_t *count);
 /* ms spent in the last call's stages, measured with CUDA events on the ctx stream.
  * out[0..7]: operation specific, see each call. */
 O3DPP_API int o3dpp_last_timings(o3dpp_ctx *ctx, double *out8);
+/* work counters of the last search when the process runs with O3DPP_STATS=1 (else zeros):
+ * [0] range-table visits [1] cell groups loaded [2] list insertions [3] candidates offered */
+O3DPP_API int o3dpp_debug_counters(o3dpp_ctx *ctx, uint64_t *out8);
 
 /* ---- cloud state: replaces o3d.utility.Vector3dVector (PointCloud.py:94-107) ----- */
 /* attr = O3DPP_ATTR_*; uploading POINTS with a different n drops normals and colours */

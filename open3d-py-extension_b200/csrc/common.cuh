@@ -80,6 +80,8 @@ struct o3dpp_ctx {
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     uint64_t launches = 0;
     double timings[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    bool want_stats = false;              // O3DPP_STATS=1: search kernels count their work
+    unsigned long long stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 
     int64_t n = 0;
     Attr3 pts, nrm, col;

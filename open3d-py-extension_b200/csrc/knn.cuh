@@ -276,6 +276,7 @@ struct KnnOut {
     int32_t *idx;               // n*K original indices (nullable)
     double *d2;                 // n*K (nullable)
     int32_t *cnt;               // n (nullable)
+    unsigned long long *stats;  // debug counters (nullable): visits, groups loaded, inserts, candidates
 };
 
 template <int S>
@@ -306,6 +307,7 @@ struct Search {
     double bound;        // prune boxes with lower bound > bound
     int home;
     Cumul cum;           // MODE 1 only: lane-private partial sums
+    unsigned st_visit, st_leaf, st_ins, st_cand;
 
     __device__ __forceinline__ Search(const GridDesc &g_) : g(g_) {}
 
@@ -352,6 +354,7 @@ struct Search {
             return;
         }
         unsigned m = __ballot_sync(FULL, v && d <= bound && (MODE != 2 || d < r2));
+        st_leaf++; st_cand += __popc(m);
         while (m) {
             int s = __ffs(m) - 1;
             m &= m - 1;
@@ -359,6 +362,7 @@ struct Search {
             int np = (int)(leaf_id * 32 + s);
             if (!key_less(nd, np, worst_d2, worst_pos, g.sidx)) continue;
             insert(nd, np);
+            st_ins++;
             refresh_worst();
             m &= __ballot_sync(FULL, d <= bound);
         }
@@ -381,6 +385,7 @@ struct Search {
         bool ex = c < g.cnt[LVL];
         double lb = ex ? box_lb(LVL, c) : pos_inf();
         unsigned m = __ballot_sync(FULL, ex && lb <= bound);
+        st_visit++;
         while (m) {
             int b = __ffs(m) - 1;
             m &= m - 1;
@@ -450,6 +455,7 @@ knn_normals_kernel(const GridDesc g, int K, double radius, KnnOut out)
     st.lane = lane; st.K = K; st.r2 = __dmul_rn(radius, radius); st.home = (int)leaf_id;
     Cumul mine;          // MODE 1: totals of the query this lane will finish
     mine.clear();
+    st.st_visit = st.st_leaf = st.st_ins = st.st_cand = 0;
 
     for (int i = 0; i < nq; ++i) {
         st.qx = shfl_d(px, i); st.qy = shfl_d(py, i); st.qz = shfl_d(pz, i);
@@ -505,6 +511,12 @@ knn_normals_kernel(const GridDesc g, int K, double radius, KnnOut out)
         }
     }
     __syncwarp();
+    if (out.stats && lane == 0) {
+        atomicAdd(out.stats + 0, (unsigned long long)st.st_visit);
+        atomicAdd(out.stats + 1, (unsigned long long)st.st_leaf);
+        atomicAdd(out.stats + 2, (unsigned long long)st.st_ins);
+        atomicAdd(out.stats + 3, (unsigned long long)st.st_cand);
+    }
     if (!valid || !out.nx) return;
     // every lane finishes one query
     double C[6];
@@ -630,6 +642,10 @@ static int search_impl(o3dpp_ctx *c, int mode, int K, double radius, bool want_n
     if (h_cnt) { O3_TRY(c->g_ncnt.ensure((size_t)n * 4 + 64)); out.cnt = c->g_ncnt.as<int32_t>(); }
     if ((h_d2 || h_cnt) && !h_idx) return set_err(O3DPP_E_ARG, "d2 / cnt need idx");
 
+    if (c->want_stats) {
+        out.stats = (unsigned long long *)(c->d_small.as<unsigned char>() + 56 * 1024);
+        CU_TRY(cudaMemsetAsync(out.stats, 0, 64, c->stream));
+    }
     GridDesc gd;
     cudaEventRecord(c->ev[0], c->stream);
     O3_TRY(grid_build(c, &gd));
@@ -644,6 +660,7 @@ static int search_impl(o3dpp_ctx *c, int mode, int K, double radius, bool want_n
     O3_TRY(d2h(c, h_idx, c->g_nbr.p, (size_t)n * K * 4));
     O3_TRY(d2h(c, h_d2, c->g_nd2.p, (size_t)n * K * 8));
     O3_TRY(d2h(c, h_cnt, c->g_ncnt.p, (size_t)n * 4));
+    if (c->want_stats) O3_TRY(d2h(c, c->stats, out.stats, 64));
     CU_TRY(cudaStreamSynchronize(c->stream));
     float a = 0, b = 0;
     cudaEventElapsedTime(&a, c->ev[0], c->ev[1]);

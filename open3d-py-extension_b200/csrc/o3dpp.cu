@@ -3,6 +3,7 @@
 //        -Xcompiler -fPIC,-ffp-contract=off,-fvisibility=hidden -shared -o libo3dpp_b200.so o3dpp.cu
 // There is no CPU path in this library: every entry point needs a live CUDA context.
 #include "ransac.cuh"
+#include <stdlib.h>
 
 #define CTX_CHECK(c)                                                      \
     do {                                                                  \
@@ -42,6 +43,8 @@ O3DPP_API int o3dpp_create(int device, o3dpp_ctx **out)
     for (int i = 0; i < 6; ++i) CU_TRY(cudaEventCreate(&c->ev[i]));
     CU_TRY(cudaHostAlloc(&c->h_small, 64 * 1024, cudaHostAllocDefault));
     O3_TRY(c->d_small.ensure(64 * 1024));
+    const char *e = getenv("O3DPP_STATS");
+    c->want_stats = e && e[0] == '1';
     *out = c;
     return 0;
 }
@@ -103,6 +106,13 @@ O3DPP_API int o3dpp_last_timings(o3dpp_ctx *c, double *out8)
 {
     if (!c || !out8) return set_err(O3DPP_E_ARG, "null argument");
     memcpy(out8, c->timings, sizeof c->timings);
+    return 0;
+}
+
+O3DPP_API int o3dpp_debug_counters(o3dpp_ctx *c, uint64_t *out8)
+{
+    if (!c || !out8) return set_err(O3DPP_E_ARG, "null argument");
+    for (int i = 0; i < 8; ++i) out8[i] = c->stats[i];
     return 0;
 }
 

@@ -24,7 +24,7 @@ MAX_KNN = 128
 SYMBOLS = [
     "o3dpp_last_error", "o3dpp_version", "o3dpp_device_count", "o3dpp_create", "o3dpp_destroy",
     "o3dpp_synchronize", "o3dpp_stream", "o3dpp_host_alloc", "o3dpp_host_free", "o3dpp_launch_count",
-    "o3dpp_last_timings", "o3dpp_upload", "o3dpp_upload_dev", "o3dpp_download", "o3dpp_download_dev",
+    "o3dpp_last_timings", "o3dpp_debug_counters", "o3dpp_upload", "o3dpp_upload_dev", "o3dpp_download", "o3dpp_download_dev",
     "o3dpp_size", "o3dpp_has", "o3dpp_drop", "o3dpp_bounds", "o3dpp_transform", "o3dpp_voxel",
     "o3dpp_voxel_fetch", "o3dpp_voxel_select", "o3dpp_estimate_normals", "o3dpp_knn",
     "o3dpp_segment_plane", "o3dpp_fetch_inliers", "o3dpp_fetch_samples", "o3dpp_select",
@@ -183,6 +183,11 @@ class Context:
     def timings(self):
         t = np.zeros(8, np.float64)
         _check(lib().o3dpp_last_timings(self._h, _ptr(t)))
+        return t
+
+    def debug_counters(self):
+        t = np.zeros(8, np.uint64)
+        _check(lib().o3dpp_debug_counters(self._h, _ptr(t)))
         return t
 
     def bounds(self):
