@@ -18,9 +18,9 @@ for rep in range(3):
 import os
 if os.environ.get('O3DPP_STATS') == '1':
     c.drop(nat.ATTR_NORMALS)
-    c.estimate_normals(0, 30, 0.0); print('stats knn per query', c.debug_counters()[:4] / N)
-    c.estimate_normals(2, 30, 0.5); print('stats hybrid per query', c.debug_counters()[:4] / N)
+    c.estimate_normals(0, 30, 0.0); print('stats knn per query', c.debug_counters()[:8] / N)
+    c.estimate_normals(2, 30, 0.5); print('stats hybrid per query', c.debug_counters()[:8] / N)
     b = np.load('tests/golden/bunny_xyz_f32.npy').astype(np.float64)
-    c.upload(nat.ATTR_POINTS, b); c.estimate_normals(0, 30, 0.0); print('bunny ms', c.timings()[:2], 'stats', c.debug_counters()[:4] / len(b))
+    c.upload(nat.ATTR_POINTS, b); c.estimate_normals(0, 30, 0.0); print('bunny ms', c.timings()[:2], 'stats', c.debug_counters()[:8] / len(b))
     u = np.random.default_rng(0).uniform(size=(1000000, 3))
-    c.upload(nat.ATTR_POINTS, u); c.estimate_normals(0, 30, 0.0); print('uniform 1M ms', c.timings()[:2], 'stats', c.debug_counters()[:4] / len(u))
+    c.upload(nat.ATTR_POINTS, u); c.estimate_normals(0, 30, 0.0); print('uniform 1M ms', c.timings()[:2], 'stats', c.debug_counters()[:8] / len(u))
