@@ -59,6 +59,7 @@ struct KfStage {
     double cc[3];               // its centre
     double rho, rho2;
     int n;                      // staged candidates
+    bool ball;                  // home box is a point: keep the points within rho of it (else: box grown by rho)
     bool overflow;
     unsigned scanned;
     __device__ __forceinline__ KfStage(const GridDesc &g_, KfWarpMem &sm_) : g(g_), sm(sm_) {}
@@ -80,9 +81,10 @@ struct KfStage {
         double lx = 0, ly = 0, lz = 0;
         if (p < g.n) {
             double x = g.sx[p], y = g.sy[p], z = g.sz[p];
-            in = x >= blo[0] - rho && x <= bhi[0] + rho && y >= blo[1] - rho && y <= bhi[1] + rho &&
-                 z >= blo[2] - rho && z <= bhi[2] + rho;
             lx = x - cc[0]; ly = y - cc[1]; lz = z - cc[2];
+            if (ball) in = (lx * lx + ly * ly) + lz * lz <= rho2;
+            else in = x >= blo[0] - rho && x <= bhi[0] + rho && y >= blo[1] - rho && y <= bhi[1] + rho &&
+                      z >= blo[2] - rho && z <= bhi[2] + rho;
         }
         unsigned m = __ballot_sync(FULL, in);
         int at = n + __popc(m & ((1u << lane) - 1u));
@@ -190,23 +192,14 @@ struct KfRows {
     float tcap;                            // largest useful threshold (hybrid: radius^2 + slack)
 };
 
-// Stage everything within `rho` (shrunk on overflow) of sg's home box.  false = cannot be staged.
+// rows are in shared memory (ncand candidates): pad the last row, give lane r the FP32 box of row r,
+// derive the error model.  rho1sq < 0 = nothing is guaranteed about what was left out.
 template <int MODE>
-__device__ __forceinline__ bool kf_stage(KfStage &sg, KfWarpMem &sm, double rho, double r2d, KfRows &R)
+__device__ __forceinline__ bool kf_rows_finish(KfWarpMem &sm, int lane, bool ok, int ncand, double rho1sq, double r2d, KfRows &R)
 {
-    const int lane = sg.lane;
-    bool ok = true;
-    for (int attempt = 0;; ++attempt) {
-        sg.n = 0; sg.overflow = false; sg.rho = rho; sg.rho2 = rho * rho * (1.0 + 1e-12);
-        sg.walk();
-        if (!sg.overflow) break;
-        if (attempt >= 8) { ok = false; break; }
-        rho *= 0.7;
-    }
-    R.ncand = ok ? sg.n : 0;
+    R.ncand = ok ? ncand : 0;
     R.nrows = (R.ncand + 31) >> 5;
-    R.rho1f = ok ? __double2float_rd(rho * rho * (1.0 - 1e-6)) : -1.0f;
-    if (!(R.rho1f > 0.0f)) ok = false;
+    R.rho1f = (ok && rho1sq > 0.0) ? __double2float_rd(rho1sq * (1.0 - 1e-6)) : -1.0f;
     if (ok) {   // pad the last row
         int padat = R.ncand + lane;
         if (padat < R.nrows * 32) { sm.x[padat] = KF_BIG; sm.y[padat] = KF_BIG; sm.z[padat] = KF_BIG; sm.pos[padat] = -1; }
@@ -239,6 +232,22 @@ __device__ __forceinline__ bool kf_stage(KfStage &sg, KfWarpMem &sm, double rho,
     return ok;
 }
 
+// Stage everything within `rho` (shrunk on overflow) of sg's home box.  false = cannot be staged.
+template <int MODE>
+__device__ __forceinline__ bool kf_stage(KfStage &sg, KfWarpMem &sm, double rho, double r2d, KfRows &R)
+{
+    bool ok = true;
+    for (int attempt = 0;; ++attempt) {
+        sg.n = 0; sg.overflow = false; sg.rho = rho; sg.rho2 = rho * rho * (1.0 + 1e-12);
+        sg.walk();
+        if (!sg.overflow) break;
+        if (attempt >= (sg.ball ? 2 : 8)) { ok = false; break; }
+        rho *= 0.7;
+    }
+    ok = kf_rows_finish<MODE>(sm, sg.lane, ok, sg.n, rho * rho, r2d, R);
+    return ok && R.rho1f > 0.0f;
+}
+
 // Select the K nearest staged candidates of the query at local (qx,qy,qz).  true = certified exact:
 // nbrow[0..cnt) holds their sorted positions.  cap (out) = upper bound of the k-th d2 when known.
 template <int MODE>
@@ -262,7 +271,7 @@ __device__ __forceinline__ bool kf_select(KfWarpMem &sm, const KfRows &R, float 
     // phase A: t with K < count(d2 <= t) <= KF_SURV
     float t = fminf(tg, R.tcap), lo = 0.f, hi = FLT_MAX;
     int c = 0;
-    bool all = false;
+    bool all = false, takeall = false;   // all: the answer is every survivor; takeall: exactly K are staged
     for (int it = 0;; ++it) {
         unsigned act = __ballot_sync(FULL, lbr <= t);
         unsigned newm = act & ~act_done;
@@ -288,6 +297,11 @@ __device__ __forceinline__ bool kf_select(KfWarpMem &sm, const KfRows &R, float 
         if (c > K && c <= KF_SURV) break;
         if (it >= 14) { st.fa++; return false; }
         if (c <= K) {
+            if (c >= R.ncand) {             // every staged candidate is already inside t
+                if (c == K || (MODE == 2 && t >= R.tcap)) { all = true; takeall = c == K && !(MODE == 2 && t >= R.tcap); break; }
+                st.fa++;
+                return false;
+            }
             if (t >= R.tcap) {
                 if (MODE == 2) { all = true; break; }
                 st.fa++;
@@ -360,7 +374,12 @@ __device__ __forceinline__ bool kf_select(KfWarpMem &sm, const KfRows &R, float 
     float af;
     if (all) {
         af = R.tcap;
-        cert = R.tcap + kf_err(R.tcap, R.eA, R.eC) <= R.rho1f;
+        if (takeall) {
+            unsigned mk = max(max(lane < c ? k0 : 0u, lane + 32 < c ? k1 : 0u), lane + 64 < c ? k2 : 0u);
+            af = __uint_as_float(__reduce_max_sync(FULL, mk));
+            cap = (double)af + (double)kf_err(af, R.eA, R.eC) * 1.0001;
+        }
+        cert = af + kf_err(af, R.eA, R.eC) <= R.rho1f;
         if (!cert) st.frho++;
     } else {
         af = __uint_as_float(akey);
@@ -383,9 +402,73 @@ __device__ __forceinline__ bool kf_select(KfWarpMem &sm, const KfRows &R, float 
     return true;
 }
 
+// Bound step of the single-query search: descend the range tables towards the entry whose farthest
+// corner is nearest to q (every entry with >= K points bounds the k-th distance by that corner), then
+// stage the three best cell groups of the last node unfiltered as rows 0..2.  Returns the staged count.
+__device__ __forceinline__ int kf_bound_rows(const GridDesc &g, KfWarpMem &sm, int lane, int K, double qx, double qy, double qz,
+                                             int64_t qpos, float *ub2_best)
+{
+    int64_t node = 0;
+    int64_t span = 32;                       // points per entry of the current table
+    for (int l = 1; l < g.levels; ++l) span *= 32;
+    unsigned pick[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu};
+    for (int lvl = g.levels - 1; lvl >= 0; --lvl, span >>= 5) {
+        int64_t c = node * 32 + lane;
+        float ub = FLT_MAX;
+        if (c < g.cnt[lvl]) {
+            int64_t have = g.n - c * span;
+            if (have > span) have = span;
+            if (have >= K) {
+                const double *b = g.box + g.off[lvl];
+                int64_t p = g.pitch[lvl];
+                double fx = fmax(qx - b[c], b[3 * p + c] - qx), fy = fmax(qy - b[p + c], b[4 * p + c] - qy), fz = fmax(qz - b[2 * p + c], b[5 * p + c] - qz);
+                ub = __double2float_ru((fx * fx + fy * fy) + fz * fz);
+            }
+        }
+        unsigned ubits = __float_as_uint(ub);
+        unsigned best = __reduce_min_sync(FULL, ubits);
+        if (best == __float_as_uint(FLT_MAX)) { *ub2_best = 0.f; break; }     // nothing holds K points (tiny cloud)
+        int bl = __ffs(__ballot_sync(FULL, ubits == best)) - 1;
+        if (lvl > 0) { node = node * 32 + bl; continue; }
+        *ub2_best = __uint_as_float(best);
+        pick[0] = (unsigned)(node * 32 + bl);
+        for (int j = 1; j < 3; ++j) {
+            if (lane == bl) ubits = 0xffffffffu;
+            best = __reduce_min_sync(FULL, ubits);
+            if (best >= __float_as_uint(FLT_MAX)) break;
+            bl = __ffs(__ballot_sync(FULL, ubits == best)) - 1;
+            pick[j] = (unsigned)(node * 32 + bl);
+        }
+    }
+    int rows = 0;
+    for (int j = 0; j < 3; ++j) {
+        if (pick[j] == 0xffffffffu) break;
+        int64_t p = (int64_t)pick[j] * 32 + lane;
+        int s = rows * 32 + lane;
+        if (p < g.n) { sm.x[s] = (float)(g.sx[p] - qx); sm.y[s] = (float)(g.sy[p] - qy); sm.z[s] = (float)(g.sz[p] - qz); sm.pos[s] = (int)p; }
+        else { sm.x[s] = KF_BIG; sm.y[s] = KF_BIG; sm.z[s] = KF_BIG; sm.pos[s] = -1; }
+        rows++;
+    }
+    // plus the 96 points around q along the curve (skipping the groups staged above: no point twice)
+    int64_t w0 = qpos - 48;
+    if (w0 + 96 > g.n) w0 = g.n - 96;
+    if (w0 < 0) w0 = 0;
+    for (int j = 0; j < 3; ++j) {
+        int64_t p = w0 + j * 32 + lane;
+        int s = rows * 32 + lane;
+        unsigned lf = (unsigned)(p >> 5);
+        bool v = p < g.n && lf != pick[0] && lf != pick[1] && lf != pick[2];
+        if (v) { sm.x[s] = (float)(g.sx[p] - qx); sm.y[s] = (float)(g.sy[p] - qy); sm.z[s] = (float)(g.sz[p] - qz); sm.pos[s] = (int)p; }
+        else { sm.x[s] = KF_BIG; sm.y[s] = KF_BIG; sm.z[s] = KF_BIG; sm.pos[s] = -1; }
+        rows++;
+    }
+    __syncwarp();
+    return rows * 32;
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(KF_WARPS * 32)
-knn_fast_kernel(const GridDesc g, int K, double radius, float rho_scale, KnnOut out)
+knn_fast_kernel(const GridDesc g, int K, double radius, float rho_scale, KnnOut out, int dbg_skip)
 {
     extern __shared__ __align__(16) unsigned char kf_smem[];
     const int lane = lane_id(), w = threadIdx.x >> 5;
@@ -405,7 +488,7 @@ knn_fast_kernel(const GridDesc g, int K, double radius, float rho_scale, KnnOut 
 
     // ---- tier 1: the whole group against one staged set ----------------------------------------
     KfStage sg(g, sm);
-    sg.lane = lane; sg.scanned = 0;
+    sg.lane = lane; sg.scanned = 0; sg.ball = false;
     {
         const double *b0 = g.box + g.off[0];
         int64_t p0 = g.pitch[0];
@@ -439,29 +522,50 @@ knn_fast_kernel(const GridDesc g, int K, double radius, float rho_scale, KnnOut 
     __syncwarp();
 
     // ---- tier 2: one failed query at a time against its own staged ball ---------------------------
+    if (dbg_skip & 1) { for (int i = 0; i < 32; ++i) if ((failed >> i & 1) && lane == 0) sm.cnt[i] = 0; failed = 0; }   // timing experiments only
     while (failed) {
         const int i = __ffs(failed) - 1;
         failed &= failed - 1;
         st.t2++;
         const double qx = shfl_d(px, i), qy = shfl_d(py, i), qz = shfl_d(pz, i);
         const double capi = shfl_d(mycap, i);
+        sg.ball = true;
         sg.blo[0] = sg.bhi[0] = sg.cc[0] = qx; sg.blo[1] = sg.bhi[1] = sg.cc[1] = qy; sg.blo[2] = sg.bhi[2] = sg.cc[2] = qz;
-        double rho_q = capi < 1e300 ? sqrt(capi) * 1.01 : 2.0 * rho_g;
+        double capq = capi;
+        if (!(dbg_skip & 4)) {   // bound step: k-th d2 among the three cell groups nearest to q (by farthest corner)
+            float ubb = 0.f;
+            int nb3 = kf_bound_rows(g, sm, lane, K, qx, qy, qz, base + i, &ubb);
+            if (nb3 > 0) {
+                KfRows Rb;
+                kf_rows_finish<MODE>(sm, lane, true, nb3, -1.0, r2d, Rb);
+                float tb = ubb > 0.f ? ubb : 1.0f;
+                double capb = pos_inf();
+                int dummy_cnt;
+                (void)kf_select<MODE>(sm, Rb, 0.f, 0.f, 0.f, K, tb, sm.nb + i * 33, &dummy_cnt, capb, st);
+                if (capb < capq) capq = capb;
+            }
+            __syncwarp();
+        }
+        double rho_q = capq < 1e300 ? sqrt(capq) * 1.01 : 2.0 * rho_g;
         if (MODE == 2 && radius * 1.001 < rho_q) rho_q = radius * 1.001;
         bool done = false;
-        if (rho_q > 0.0) {
+        if (rho_q > 0.0 && !(dbg_skip & 2)) {
             for (int attempt = 0; attempt < 3 && !done; ++attempt) {
                 KfRows Rq;
                 if (!kf_stage<MODE>(sg, sm, rho_q, r2d, Rq)) break;
-                float t2 = capi < 1e300 ? (float)capi : 0.25f * Rq.rho1f;
+                float t2 = capq < 1e300 ? (float)capq * fminf(1.0f, 56.0f / (float)(Rq.ncand > 0 ? Rq.ncand : 1)) : 0.25f * Rq.rho1f;
                 double cap2 = pos_inf();
                 done = kf_select<MODE>(sm, Rq, 0.f, 0.f, 0.f, K, t2, sm.nb + i * 33, sm.cnt + i, cap2, st);
-                if (MODE == 2 && rho_q >= radius) break;   // the radius ball was staged in full: growing cannot help
+                if ((dbg_skip & 8) && lane == 0 && leaf_id % 499 == 0)
+                    printf("t2 leaf %lld q %d att %d capi %.4g capq %.4g rho_q %.4g -> rho1f %.4g ncand %d rows %d done %d cap2 %.4g scanned_total %u\n",
+                           (long long)leaf_id, i, attempt, capi, capq, rho_q, (double)Rq.rho1f, Rq.ncand, Rq.nrows, (int)done, cap2, sg.scanned);
+                if (capq < 1e300) break;                   // the ball of a valid bound holds the answer: growing cannot help
+                if (MODE == 2 && rho_q >= radius) break;   // the radius ball was staged in full
                 rho_q *= 2.0;
             }
         }
         if (!done) {
-            kf_slow_query<MODE>(g, leaf_id, i, K, r2d, capi, out);   // tier 3 finishes the query itself
+            kf_slow_query<MODE>(g, leaf_id, i, K, r2d, capq, out);   // tier 3 finishes the query itself
             if (lane == 0) sm.cnt[i] = -1;
             st.slow++;
         }
@@ -507,7 +611,9 @@ static int launch_fast(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, c
     int64_t blocks = (gd.cnt[0] + KF_WARPS - 1) / KF_WARPS;
     float rho = 0.5f;
     if (const char *e = getenv("O3DPP_KNN_RHO")) { float v = (float)atof(e); if (v > 0.f) rho = v; }
-    LAUNCH(c, kern, (int)blocks, KF_WARPS * 32, smem, gd, K, radius, rho, out);
+    int dbg = 0;
+    if (const char *e = getenv("O3DPP_KNN_DEBUG_SKIP")) dbg = atoi(e);   // 1: drop failed queries, 2: no tier 2 (timing experiments)
+    LAUNCH(c, kern, (int)blocks, KF_WARPS * 32, smem, gd, K, radius, rho, out, dbg);
     return check_launch("knn_fast");
 }
 
