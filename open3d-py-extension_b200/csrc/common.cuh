@@ -81,7 +81,7 @@ struct o3dpp_ctx {
     uint64_t launches = 0;
     double timings[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     bool want_stats = false;              // O3DPP_STATS=1: search kernels count their work
-    unsigned long long stats[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    unsigned long long stats[32] = {0};
 
     int64_t n = 0;
     Attr3 pts, nrm, col;

@@ -1,0 +1,167 @@
+// knn_host.cuh — host side of the neighbour search: picks the kernel tier chain and launches it.
+#pragma once
+#include "knn_lane.cuh"
+
+// ---- host side -----------------------------------------------------------------------------------
+template <int MODE>
+static int launch_fast(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, const KnnOut &out)
+{
+    size_t smem = (size_t)KF_WARPS * sizeof(KfWarpMem);
+    auto kern = knn_fast_kernel<MODE>;
+    if (smem > 48 * 1024) CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t blocks = (gd.cnt[0] + KF_WARPS - 1) / KF_WARPS;
+    float rho = 0.5f;
+    if (const char *e = getenv("O3DPP_KNN_RHO")) { float v = (float)atof(e); if (v > 0.f) rho = v; }
+    int dbg = 0;
+    if (const char *e = getenv("O3DPP_KNN_DEBUG_SKIP")) dbg = atoi(e);   // 1: drop failed queries, 2: no tier 2 (timing experiments)
+    LAUNCH(c, kern, (int)blocks, KF_WARPS * 32, smem, gd, K, radius, rho, out, dbg);
+    return check_launch("knn_fast");
+}
+
+struct CapPending {
+    const float *cap;
+    __device__ __forceinline__ bool operator()(int64_t i) const { return cap[i] >= 0.0f; }
+};
+
+// tier chain of the lane-per-query path (knn_lane.cuh): tier 1 over every cell group, then the queries it
+// could not certify, compacted in curve order, through the FP64 range query and the exact list search
+template <int MODE>
+static int launch_lane(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, const KnnOut &out)
+{
+    int64_t n = gd.n;
+    O3_TRY(c->g_ncnt.ensure((size_t)n * 4 + 64));
+    O3_TRY(c->g_nbr.ensure((size_t)n * 4 + 64));
+    float *capbuf = c->g_ncnt.as<float>();
+    int32_t *list = c->g_nbr.as<int32_t>();
+    size_t smem = (size_t)KL_WARPS * sizeof(KlWarpMem);
+    auto k1 = knn_lane_kernel<MODE>;
+    CU_TRY(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t blocks = (gd.cnt[0] + KL_WARPS - 1) / KL_WARPS;
+    float rho = 0.5f;
+    if (const char *e = getenv("O3DPP_KNN_RHO")) { float v = (float)atof(e); if (v > 0.f) rho = v; }
+    cudaEventRecord(c->ev[3], c->stream);
+    LAUNCH(c, k1, (int)blocks, KL_WARPS * 32, smem, gd, K, radius, rho, out, capbuf);
+    O3_TRY(check_launch("knn_lane"));
+    cudaEventRecord(c->ev[4], c->stream);
+    int64_t m2 = 0, m3 = 0;
+    CapPending pred{capbuf};
+    O3_TRY(compact_indices(c, pred, n, list, &m2));
+    if (m2 > 0) {
+        size_t smem2 = (size_t)K2_LIST * K2_THREADS * 12;
+        auto k2 = knn_range_kernel<MODE>;
+        CU_TRY(cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+        LAUNCH(c, k2, (int)((m2 + K2_THREADS - 1) / K2_THREADS), K2_THREADS, smem2, gd, K, radius, out, list, (int)m2, capbuf);
+        O3_TRY(check_launch("knn_range"));
+        cudaEventRecord(c->ev[5], c->stream);
+        O3_TRY(compact_indices(c, pred, n, list, &m3));
+        if (m3 > 0) {
+            auto k3 = knn_exact_kernel<MODE>;
+            LAUNCH(c, k3, (int)((m3 + 3) / 4), 128, 0, gd, K, radius, out, list, (int)m3, capbuf);
+            O3_TRY(check_launch("knn_exact"));
+        }
+    } else cudaEventRecord(c->ev[5], c->stream);
+    c->timings[4] = (double)m2;
+    c->timings[5] = (double)m3;
+    return 0;
+}
+
+template <int MODE, int S, int WARPS>
+static int launch_search(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, const KnnOut &out)
+{
+    size_t smem = (size_t)WARPS * 32 * (32 * S + 1) * sizeof(int);
+    auto kern = knn_normals_kernel<MODE, S, WARPS>;
+    if (smem > 48 * 1024) CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t blocks = (gd.cnt[0] + WARPS - 1) / WARPS;
+    LAUNCH(c, kern, (int)blocks, WARPS * 32, smem, gd, K, radius, out);
+    return check_launch("knn_normals");
+}
+
+template <int MODE>
+static int launch_search_mode(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, const KnnOut &out)
+{
+    if (MODE == 1 || K <= 32) return launch_search<MODE, 1, 4>(c, gd, K, radius, out);
+    if (K <= 64) return launch_search<MODE, 2, 4>(c, gd, K, radius, out);
+    return launch_search<MODE, 4, 2>(c, gd, K, radius, out);
+}
+
+static int search_impl(o3dpp_ctx *c, int mode, int K, double radius, bool want_normals, int32_t *h_idx,
+                       double *h_d2, int32_t *h_cnt)
+{
+    int64_t n = c->n;
+    if (mode < 0 || mode > 2) return set_err(O3DPP_E_ARG, "unknown search mode");
+    if (mode != O3DPP_SEARCH_RADIUS) {
+        if (K <= 0) return set_err(O3DPP_E_ARG, "knn must be positive");
+        if (K > O3DPP_MAX_KNN) return set_err(O3DPP_E_UNSUPPORTED, "knn larger than O3DPP_MAX_KNN");
+    } else {
+        if (h_idx || h_d2) return set_err(O3DPP_E_UNSUPPORTED, "radius search returns counts only");
+        K = 1;
+    }
+    if (mode != O3DPP_SEARCH_KNN && !(radius >= 0.0)) return set_err(O3DPP_E_ARG, "radius must be >= 0");
+    if (n == 0) return 0;
+    KnnOut out;
+    memset(&out, 0, sizeof out);
+    if (want_normals) {
+        out.has_old_normals = c->nrm.present ? 1 : 0;
+        if (!c->nrm.present) O3_TRY(attr_alloc(&c->nrm, n));
+        out.nx = c->nrm.x(); out.ny = c->nrm.y(); out.nz = c->nrm.z();
+    }
+    if (h_idx) { O3_TRY(c->g_nbr.ensure((size_t)n * K * 4 + 64)); out.idx = c->g_nbr.as<int32_t>(); }
+    if (h_d2) { O3_TRY(c->g_nd2.ensure((size_t)n * K * 8 + 64)); out.d2 = c->g_nd2.as<double>(); }
+    if (h_cnt) { O3_TRY(c->g_ncnt.ensure((size_t)n * 4 + 64)); out.cnt = c->g_ncnt.as<int32_t>(); }
+    if ((h_d2 || h_cnt) && !h_idx) return set_err(O3DPP_E_ARG, "d2 / cnt need idx");
+
+    if (c->want_stats) {
+        out.stats = (unsigned long long *)(c->d_small.as<unsigned char>() + 56 * 1024);
+        CU_TRY(cudaMemsetAsync(out.stats, 0, 256, c->stream));
+    }
+    GridDesc gd;
+    cudaEventRecord(c->ev[0], c->stream);
+    O3_TRY(grid_build(c, &gd));
+    cudaEventRecord(c->ev[1], c->stream);
+    int rc;
+    // estimate_normals with k <= 32 takes the certified FP32 selection kernel; searches that must
+    // return sorted (d2, index) lists, k > 32 and pure radius search use the FP64 list kernel
+    static const bool force_list = getenv("O3DPP_KNN_LIST") != nullptr;
+    bool fast = want_normals && !h_idx && K <= 32 && mode != O3DPP_SEARCH_RADIUS && !force_list;
+    static const bool old_fast = getenv("O3DPP_KNN_WARPSELECT") != nullptr;   // previous generation, kept for A/B timing
+    if (fast && !old_fast) rc = mode == 0 ? launch_lane<0>(c, gd, K, radius, out) : launch_lane<2>(c, gd, K, radius, out);
+    else if (fast) rc = mode == 0 ? launch_fast<0>(c, gd, K, radius, out) : launch_fast<2>(c, gd, K, radius, out);
+    else if (mode == 0) rc = launch_search_mode<0>(c, gd, K, radius, out);
+    else if (mode == 1) rc = launch_search_mode<1>(c, gd, K, radius, out);
+    else rc = launch_search_mode<2>(c, gd, K, radius, out);
+    if (rc) return rc;
+    cudaEventRecord(c->ev[2], c->stream);
+    if (want_normals) c->nrm.present = true;
+    O3_TRY(d2h(c, h_idx, c->g_nbr.p, (size_t)n * K * 4));
+    O3_TRY(d2h(c, h_d2, c->g_nd2.p, (size_t)n * K * 8));
+    O3_TRY(d2h(c, h_cnt, c->g_ncnt.p, (size_t)n * 4));
+    if (c->want_stats) O3_TRY(d2h(c, c->stats, out.stats, 256));
+    CU_TRY(cudaStreamSynchronize(c->stream));
+    float a = 0, b = 0;
+    cudaEventElapsedTime(&a, c->ev[0], c->ev[1]);
+    cudaEventElapsedTime(&b, c->ev[1], c->ev[2]);
+    c->timings[0] = a;
+    c->timings[1] = b;
+    if (fast && !old_fast) {
+        float t1 = 0, t2 = 0;
+        cudaEventElapsedTime(&t1, c->ev[3], c->ev[4]);
+        cudaEventElapsedTime(&t2, c->ev[4], c->ev[2]);
+        c->timings[2] = t1;     // tier 1 kernel
+        c->timings[3] = t2;     // compaction + tiers 2 and 3
+        if (c->want_stats && c->stats[16]) {
+            double nq = (double)n, nw = (double)c->stats[16];
+            fprintf(stderr, "[o3dpp lane] n=%lld mode=%d K=%d tier1 %.3f ms, tiers2+3 %.3f ms (tier2 %lld, tier3 %lld queries) | per warp: candidates %.1f "
+                    "groups-scanned %.1f restages %.3f | fail per query: gap %.4f rho %.4f boundary %.4f count %.4f warp %.4f\n", (long long)n, mode, K,
+                    t1, t2, (long long)c->timings[4], (long long)c->timings[5], c->stats[17] / nw, c->stats[18] / nw, c->stats[24] / nw,
+                    c->stats[19] / nq, c->stats[20] / nq, c->stats[21] / nq, c->stats[22] / nq, c->stats[23] / nq);
+        }
+    }
+    if (c->want_stats) {
+        double nq = (double)n, nw = (double)((n + 31) / 32);
+        fprintf(stderr, "[o3dpp stats] n=%lld mode=%d K=%d ms=%.3f | per query: slow %.4f roundsA %.2f roundsC %.2f failwarp %.4f failA %.4f failC %.4f "
+                "failgap %.4f failrho %.4f active-rows %.2f tier2 %.4f | per warp: rows %.2f groups-scanned %.2f\n", (long long)n, mode, K, b,
+                c->stats[4] / nq, c->stats[6] / nq, c->stats[7] / nq, c->stats[8] / nq, c->stats[9] / nq, c->stats[10] / nq,
+                c->stats[11] / nq, c->stats[12] / nq, c->stats[14] / nq, c->stats[15] / nq, c->stats[5] / nw, c->stats[13] / nw);
+    }
+    return 0;
+}

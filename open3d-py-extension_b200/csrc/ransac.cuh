@@ -11,7 +11,7 @@
 //   select  : the host replays Open3D's serial best-so-far / early-exit rule over the scores
 //   final   : ordered compaction of the winner's inliers + two reduction passes for the refit
 #pragma once
-#include "knn_fast.cuh"
+#include "knn_host.cuh"
 #include <random>
 
 #define PHILOX_TAG 0x52414E53u /* "RANS" */

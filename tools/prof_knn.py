@@ -11,4 +11,4 @@ c.upload(nat.ATTR_POINTS, pts)
 for _ in range(2):
     c.drop(nat.ATTR_NORMALS)
     c.estimate_normals(mode, 30, 0.5 if mode == 2 else 0.0)
-    print('ms', c.timings()[:2])
+    print('ms', [round(v, 3) for v in c.timings()[:6]])
