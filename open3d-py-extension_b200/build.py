@@ -40,12 +40,14 @@ def nvcc():
     return "nvcc"
 
 
-def build(force=False, verbose=False):
-    if not force and not stale():
+def build(force=False, verbose=False, out=None, defines=()):
+    """out / defines: tuning builds (tools/variants.py), e.g. defines=("KL_WARPS=2",) into another file"""
+    if out is None and not force and not stale():
         return LIB
-    cmd = [nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB, os.path.join(CSRC, "o3dpp.cu")]
+    out = out or LIB
+    cmd = [nvcc()] + NVCC_FLAGS + [f"-D{d}" for d in defines] + (["-Xptxas", "-v"] if verbose else []) + ["-o", out, os.path.join(CSRC, "o3dpp.cu")]
     subprocess.check_call(cmd, cwd=CSRC)
-    return LIB
+    return out
 
 
 if __name__ == "__main__":

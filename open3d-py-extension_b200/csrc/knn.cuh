@@ -209,7 +209,7 @@ __device__ __forceinline__ void eig_vec1(const double *A, const double *e0, doub
     }
 }
 
-__device__ void fast_eigen3x3(const double *C, double *out)
+__device__ __forceinline__ void fast_eigen3x3(const double *C, double *out)
 {
     double mc = C[0];
 #pragma unroll

@@ -37,7 +37,7 @@ static int launch_lane(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, c
     auto k1 = knn_lane_kernel<MODE>;
     CU_TRY(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int64_t blocks = (gd.cnt[0] + KL_WARPS - 1) / KL_WARPS;
-    float rho = 0.5f;
+    float rho = 0.4f;          // staging radius / part-box diagonal (measured optimum on the LiDAR-like scans)
     if (const char *e = getenv("O3DPP_KNN_RHO")) { float v = (float)atof(e); if (v > 0.f) rho = v; }
     cudaEventRecord(c->ev[3], c->stream);
     LAUNCH(c, k1, (int)blocks, KL_WARPS * 32, smem, gd, K, radius, rho, out, capbuf);
@@ -47,10 +47,9 @@ static int launch_lane(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, c
     CapPending pred{capbuf};
     O3_TRY(compact_indices(c, pred, n, list, &m2));
     if (m2 > 0) {
-        size_t smem2 = (size_t)K2_LIST * K2_THREADS * 12;
         auto k2 = knn_range_kernel<MODE>;
-        CU_TRY(cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-        LAUNCH(c, k2, (int)((m2 + K2_THREADS - 1) / K2_THREADS), K2_THREADS, smem2, gd, K, radius, out, list, (int)m2, capbuf);
+        int64_t warps2 = (m2 + 31) / 32;
+        LAUNCH(c, k2, (int)((warps2 + K2_WARPS - 1) / K2_WARPS), K2_WARPS * 32, 0, gd, K, radius, out, list, (int)m2, capbuf);
         O3_TRY(check_launch("knn_range"));
         cudaEventRecord(c->ev[5], c->stream);
         O3_TRY(compact_indices(c, pred, n, list, &m3));
@@ -145,14 +144,17 @@ static int search_impl(o3dpp_ctx *c, int mode, int K, double radius, bool want_n
     if (fast && !old_fast) {
         float t1 = 0, t2 = 0;
         cudaEventElapsedTime(&t1, c->ev[3], c->ev[4]);
-        cudaEventElapsedTime(&t2, c->ev[4], c->ev[2]);
+        float t3 = 0;
+        cudaEventElapsedTime(&t2, c->ev[4], c->ev[5]);
+        cudaEventElapsedTime(&t3, c->ev[5], c->ev[2]);
         c->timings[2] = t1;     // tier 1 kernel
-        c->timings[3] = t2;     // compaction + tiers 2 and 3
+        c->timings[3] = t2;     // compaction + tier 2
+        c->timings[6] = t3;     // compaction + tier 3
         if (c->want_stats && c->stats[16]) {
             double nq = (double)n, nw = (double)c->stats[16];
-            fprintf(stderr, "[o3dpp lane] n=%lld mode=%d K=%d tier1 %.3f ms, tiers2+3 %.3f ms (tier2 %lld, tier3 %lld queries) | per warp: candidates %.1f "
+            fprintf(stderr, "[o3dpp lane] n=%lld mode=%d K=%d tier1 %.3f ms, tier2 %.3f ms, tier3 %.3f ms (tier2 %lld, tier3 %lld queries) | per warp: parts %.3f candidates %.1f "
                     "groups-scanned %.1f restages %.3f | fail per query: gap %.4f rho %.4f boundary %.4f count %.4f warp %.4f\n", (long long)n, mode, K,
-                    t1, t2, (long long)c->timings[4], (long long)c->timings[5], c->stats[17] / nw, c->stats[18] / nw, c->stats[24] / nw,
+                    t1, t2, t3, (long long)c->timings[4], (long long)c->timings[5], c->stats[25] / nw, c->stats[17] / nw, c->stats[18] / nw, c->stats[24] / nw,
                     c->stats[19] / nq, c->stats[20] / nq, c->stats[21] / nq, c->stats[22] / nq, c->stats[23] / nq);
         }
     }

@@ -21,18 +21,41 @@
 #pragma once
 #include "knn_fast.cuh"
 
-#define KL_WARPS 4
+#ifndef KL_WARPS
+#define KL_WARPS 1
+#endif
+#ifndef KL_CAP
 #define KL_CAP 768      // staged candidates per warp
+#endif
+#ifndef KL_NB
 #define KL_NB 32        // histogram bins
-#define KL_BND 16       // boundary-bin list entries per query
+#endif
+#ifndef KL_GMAX
+#define KL_GMAX 512     // cell groups one part may scan
+#endif
+#ifndef KL_GSPLIT
+#define KL_GSPLIT 192   // more groups than this to scan: split the part without trying
+#endif
+#ifndef KL_UNR
+#define KL_UNR 4       // candidates per iteration of the two select passes
+#endif
+#ifndef KL_MINB
+#define KL_MINB 12
+#endif
+#ifndef KL_BND
+#define KL_BND 24       // boundary-bin list entries per query
+#endif
 
 struct KlWarpMem {
-    float4 cand[KL_CAP];
+    float4 cand[KL_CAP + 8];
     union {
-        unsigned hist[KL_NB * 32];                                           // [bin][lane]
+        unsigned hist[(KL_NB + 1) * 32];                                        // [bin][lane]
         struct { float d[KL_BND * 32]; unsigned short s[KL_BND * 32]; } bnd; // [entry][lane]
     } u;
-    unsigned short nb[32 * 32];                                              // [j][lane] staged slots
+    union {
+        unsigned short nb[32 * 32];                                          // [j][lane] staged slots
+        unsigned gl[KL_GMAX];                                                // cell groups to scan (stage only)
+    } v;
 };
 
 struct KlStage {
@@ -42,8 +65,7 @@ struct KlStage {
     int64_t home;
     double blo[3], bhi[3], cc[3];
     double rho, rho2;
-    int n;
-    bool overflow;
+    int n, ngroups;
     unsigned scanned;
     __device__ __forceinline__ KlStage(const GridDesc &g_, KlWarpMem &sm_) : g(g_), sm(sm_) {}
 
@@ -57,23 +79,415 @@ struct KlStage {
         return (gx * gx + gy * gy) + gz * gz;
     }
 
-    __device__ __forceinline__ void scan_group(int64_t leaf)
+    // phase 1: the cell groups whose box comes within rho of the part's box (the home group is staged already)
+    template <int LVL>
+    __device__ __forceinline__ void collect(int64_t parent)
     {
-        int64_t p = leaf * 32 + lane;
-        bool in = false;
-        double lx = 0, ly = 0, lz = 0;
-        if (p < g.n) {
-            double x = g.sx[p], y = g.sy[p], z = g.sz[p];
-            lx = x - cc[0]; ly = y - cc[1]; lz = z - cc[2];
-            in = x >= blo[0] - rho && x <= bhi[0] + rho && y >= blo[1] - rho && y <= bhi[1] + rho &&
-                 z >= blo[2] - rho && z <= bhi[2] + rho;
+        int64_t c = parent * 32 + lane;
+        bool ex = c < g.cnt[LVL];
+        double gp = ex ? gap(LVL, c) : pos_inf();
+        if constexpr (LVL == 0) {
+            bool take = ex && gp <= rho2 && c != home;
+            unsigned m = __ballot_sync(FULL, take);
+            int at = ngroups + __popc(m & ((1u << lane) - 1u));
+            if (take && at < KL_GMAX) sm.v.gl[at] = (unsigned)c;
+            ngroups += __popc(m);
+        } else {
+            unsigned m = __ballot_sync(FULL, ex && gp <= rho2);
+            while (m && ngroups <= KL_GSPLIT) {
+                int b = __ffs(m) - 1;
+                m &= m - 1;
+                collect<LVL - 1>(parent * 32 + b);
+            }
         }
+    }
+
+    __device__ __forceinline__ void append(int64_t p, double x, double y, double z)
+    {
+        bool in = p < g.n && x >= blo[0] - rho && x <= bhi[0] + rho && y >= blo[1] - rho && y <= bhi[1] + rho &&
+                  z >= blo[2] - rho && z <= bhi[2] + rho;
         unsigned m = __ballot_sync(FULL, in);
         int at = n + __popc(m & ((1u << lane) - 1u));
-        if (in && at < KL_CAP) sm.cand[at] = make_float4((float)lx, (float)ly, (float)lz, __int_as_float((int)p));
+        if (in && at < KL_CAP)
+            sm.cand[at] = make_float4((float)(x - cc[0]), (float)(y - cc[1]), (float)(z - cc[2]), __int_as_float((int)p));
         n += __popc(m);
-        if (n > KL_CAP) overflow = true;
-        scanned++;
+    }
+
+    // phase 2: scan the collected groups, four at a time so that twelve loads are in flight per lane.
+    // false = the staging area overflowed or there are too many groups (the caller splits the part).
+    __device__ __forceinline__ bool stage()
+    {
+        ngroups = 0;
+        switch (g.levels - 1) {
+        case 0: collect<0>(0); break;
+        case 1: collect<1>(0); break;
+        case 2: collect<2>(0); break;
+        case 3: collect<3>(0); break;
+        case 4: collect<4>(0); break;
+        default: collect<5>(0); break;
+        }
+        if (ngroups > KL_GSPLIT) return false;
+        __syncwarp();
+        n = 32;
+        const int64_t last = g.n - 1;
+        for (int i = 0; i < ngroups; i += 4) {
+            int64_t p[4];
+            double x[4], y[4], z[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                p[k] = i + k < ngroups ? (int64_t)sm.v.gl[i + k] * 32 + lane : g.n;
+                int64_t q = p[k] < last ? p[k] : last;
+                x[k] = g.sx[q]; y[k] = g.sy[q]; z[k] = g.sz[q];
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) append(p[k], x[k], y[k], z[k]);
+            scanned += 4;
+            if (n > KL_CAP) return false;
+        }
+        return true;
+    }
+};
+
+__device__ __forceinline__ float kl_d2(const float4 c, float qx, float qy, float qz)
+{
+    float dx = c.x - qx, dy = c.y - qy, dz = c.z - qz;
+    return fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+}
+
+// quarter-octave bin of a non-negative float relative to `base` (the bits of d2 >> 21 keep the exponent and
+// two mantissa bits): monotone in d2, three integer instructions
+__device__ __forceinline__ int kl_bin(float d, int base)
+{
+    int b = (__float_as_int(d) >> 21) - base;
+    return min(max(b, 0), KL_NB);          // KL_NB = beyond the range (its counter is never read)
+}
+
+// what one lane learnt about its query
+struct KlAnswer {
+    bool ok;          // certified: sm.v.nb[.][lane] holds cn staged slots
+    int cn;
+    float capf;       // upper bound of the true k-th d2 when not certified (+inf: none)
+    unsigned why;     // 1 gap, 2 rho, 3 boundary overflow, 4 count, 5 not staged
+};
+
+// SELECT + CERTIFY of every lane's own query against the np staged candidates (np % 4 == 0).
+// T = histogram range (an upper bound of the k-th d2 of the staged set, or the hybrid radius cap).
+template <int MODE>
+__device__ __forceinline__ KlAnswer kl_select(KlWarpMem &sm, int lane, int np, int K, float qx, float qy, float qz, float U,
+                                              float tcap, float rho1f, float eA, float eC)
+{
+    KlAnswer A;
+    A.ok = false; A.cn = 0; A.why = 0;
+    const float4 *cd = sm.cand;
+    float T = U;
+    bool capped = false;
+    if (MODE == 2 && tcap < T) { T = tcap; capped = true; }
+    const bool dead = !(T > 1e-36f);
+    const int base = (__float_as_int(dead ? 1.0f : T) >> 21) - (KL_NB - 1);
+    unsigned *hist = sm.u.hist + lane;
+#pragma unroll
+    for (int b = 0; b < KL_NB; ++b) hist[b * 32] = 0u;
+    // pass B: lane-private histogram of d2 (candidates are broadcast reads, loads issued ahead of the updates)
+    for (int s = 0; s < np; s += KL_UNR) {
+        float4 cc[KL_UNR];
+        int bb[KL_UNR];
+#pragma unroll
+        for (int u = 0; u < KL_UNR; ++u) cc[u] = cd[s + u];
+#pragma unroll
+        for (int u = 0; u < KL_UNR; ++u) bb[u] = kl_bin(kl_d2(cc[u], qx, qy, qz), base);
+#pragma unroll
+        for (int u = 0; u < KL_UNR; ++u) atomicAdd(hist + bb[u] * 32, 1u);
+    }
+    int c0 = 0, bstar = -1, cb = 0, acc = 0;
+#pragma unroll
+    for (int b = 0; b < KL_NB; ++b) {
+        int h = (int)hist[b * 32];
+        if (bstar < 0 && acc + h >= K) { bstar = b; c0 = acc; cb = h; }
+        acc += h;
+    }
+    const bool takeall = bstar < 0 && MODE == 2 && capped;   // fewer than K inside the radius
+    const bool counted = bstar >= 0;
+    if (takeall) bstar = KL_NB;
+    const int beq = (takeall || cb > KL_BND) ? -1 : bstar;   // a boundary bin too full for the list fails below
+    __syncwarp();     // the boundary lists alias the histograms of other lanes
+    // pass C: candidates below bin b* are neighbours (fewer than K of them), those inside it go to the
+    // boundary list (at most KL_BND), the smallest d2 above it is tracked
+    float bmin = KF_HUGE;
+    float *bd = sm.u.bnd.d + lane, *bdp = bd;
+    unsigned short *bs = sm.u.bnd.s + lane, *bsp = bs, *nbp = sm.v.nb + lane;
+    for (int s = 0; s < np; s += KL_UNR) {
+        float4 cc[KL_UNR];
+        float dd[KL_UNR];
+        int bb[KL_UNR];
+#pragma unroll
+        for (int u = 0; u < KL_UNR; ++u) cc[u] = cd[s + u];
+#pragma unroll
+        for (int u = 0; u < KL_UNR; ++u) { dd[u] = kl_d2(cc[u], qx, qy, qz); bb[u] = kl_bin(dd[u], base); }
+#pragma unroll
+        for (int u = 0; u < KL_UNR; ++u) {
+            if (bb[u] < bstar) { *nbp = (unsigned short)(s + u); nbp += 32; }
+            else if (bb[u] == beq) { *bdp = dd[u]; *bsp = (unsigned short)(s + u); bdp += 32; bsp += 32; }
+            else bmin = fminf(bmin, dd[u]);
+        }
+    }
+    const float ubound = U + kf_err(U, eA, eC) * 1.0001f;
+    if (dead) { A.why = 4; A.capf = ubound; }
+    else if (takeall) {
+        A.ok = tcap + kf_err(tcap, eA, eC) <= rho1f;
+        A.capf = tcap;
+        if (!A.ok) A.why = 2;
+    } else if (!counted) { A.why = 4; A.capf = ubound; }
+    else if (cb > KL_BND) {
+        A.why = 3;
+        float edge = __int_as_float((bstar + base + 1) << 21);      // every d2 of bins <= b* is below it
+        A.capf = fminf(ubound, edge + kf_err(edge, eA, eC) * 1.0001f);
+    } else {
+        const int need = K - c0;
+        float a = 0.f;
+        for (int r = 0; r < need; ++r) {
+            float best = KF_HUGE;
+            int be = 0;
+            for (int e = 0; e < cb; ++e) { float v = bd[e * 32]; if (v < best) { best = v; be = e; } }
+            a = best;
+            *nbp = bs[be * 32];
+            nbp += 32;
+            bd[be * 32] = KF_HUGE;
+        }
+        float rest = bmin;
+        for (int e = 0; e < cb; ++e) rest = fminf(rest, bd[e * 32]);
+        const float ea = kf_err(a, eA, eC);
+        const bool c1 = rest - a > 2.0f * kf_err(rest, eA, eC), c2 = a + ea <= rho1f;
+        A.ok = c1 && c2;
+        A.capf = a + ea * 1.0001f;
+        if (!c1) A.why = 1; else if (!c2) A.why = 2;
+    }
+    A.cn = (int)(nbp - (sm.v.nb + lane)) >> 5;
+    return A;
+}
+
+
+// stats slots (out.stats, O3DPP_STATS=1): 16 warps, 17 candidates, 18 groups scanned, 19 fail-gap,
+// 20 fail-rho, 21 fail-boundary-overflow, 22 fail-count, 23 fail-not-staged, 24 restages, 25 parts
+template <int MODE>
+__global__ void __launch_bounds__(KL_WARPS * 32, KL_MINB)
+knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, KnnOut out, float *__restrict__ capbuf)
+{
+    extern __shared__ __align__(16) unsigned char kl_smem[];
+    const int lane = lane_id(), w = threadIdx.x >> 5;
+    const int64_t leaf_id = (int64_t)blockIdx.x * KL_WARPS + w;
+    if (leaf_id >= g.cnt[0]) return;
+    KlWarpMem &sm = ((KlWarpMem *)kl_smem)[w];
+    const int64_t base = leaf_id * 32;
+    const int nq = (int)(g.n - base < 32 ? g.n - base : 32);
+    const int64_t mypos = base + lane;
+    const bool valid = lane < nq;
+    const double r2d = __dmul_rn(radius, radius);
+    double px = 0, py = 0, pz = 0;
+    if (valid) { px = g.sx[mypos]; py = g.sy[mypos]; pz = g.sz[mypos]; }
+
+    KlStage sg(g, sm);
+    sg.lane = lane; sg.scanned = 0; sg.home = leaf_id;
+    // the home box; candidate coordinates are relative to its centre for every part of the group
+    double hlo[3], hhi[3];
+    {
+        const double *b0 = g.box + g.off[0];
+        int64_t p0 = g.pitch[0];
+        hlo[0] = b0[leaf_id]; hlo[1] = b0[p0 + leaf_id]; hlo[2] = b0[2 * p0 + leaf_id];
+        hhi[0] = b0[3 * p0 + leaf_id]; hhi[1] = b0[4 * p0 + leaf_id]; hhi[2] = b0[5 * p0 + leaf_id];
+    }
+    sg.cc[0] = 0.5 * (hlo[0] + hhi[0]); sg.cc[1] = 0.5 * (hlo[1] + hhi[1]); sg.cc[2] = 0.5 * (hlo[2] + hhi[2]);
+    const double hext = fmax(fmax(hhi[0] - hlo[0], hhi[1] - hlo[1]), hhi[2] - hlo[2]);
+    // own query in local FP32; the home group occupies slots 0..31 (bit-identical to the query copies)
+    const float qx = valid ? (float)(px - sg.cc[0]) : KF_BIG, qy = valid ? (float)(py - sg.cc[1]) : KF_BIG,
+                qz = valid ? (float)(pz - sg.cc[2]) : KF_BIG;
+    sm.cand[lane] = make_float4(qx, qy, qz, __int_as_float(valid ? (int)mypos : -1));
+    __syncwarp();
+    // U = largest d2 to a member of the home group: bounds the k-th d2 when the group holds >= K points
+    float U = 0.f;
+#pragma unroll 8
+    for (int s = 0; s < 32; ++s) {
+        float d = kl_d2(sm.cand[s], qx, qy, qz);
+        if (s < nq) U = fmaxf(U, d);
+    }
+    unsigned restage = 0, parts = 0, candsum = 0;
+    unsigned n1 = 0, n2 = 0, n3 = 0, n4 = 0, n5 = 0;
+
+    // parts of the group: [start, start + len), len a power of two; a part whose grown box overflows the
+    // staging area is halved (mixed-density groups), so every block of lanes is staged at most once
+    int start = 0, len = 32;
+    while (start < nq) {
+        const bool inpart = lane >= start && lane < start + len;
+        if (len == 32) {
+#pragma unroll
+            for (int a = 0; a < 3; ++a) { sg.blo[a] = hlo[a]; sg.bhi[a] = hhi[a]; }
+        } else {
+            const double INF = pos_inf();
+            const bool v = inpart && valid;
+            sg.blo[0] = warp_min_d(v ? px : INF); sg.blo[1] = warp_min_d(v ? py : INF); sg.blo[2] = warp_min_d(v ? pz : INF);
+            sg.bhi[0] = warp_max_d(v ? px : -INF); sg.bhi[1] = warp_max_d(v ? py : -INF); sg.bhi[2] = warp_max_d(v ? pz : -INF);
+        }
+        const double ex = sg.bhi[0] - sg.blo[0], ey = sg.bhi[1] - sg.blo[1], ez = sg.bhi[2] - sg.blo[2];
+        double rho = sqrt((ex * ex + ey * ey) + ez * ez) * (double)rho_scale;
+        if (len < 32) rho *= 1.25;          // smaller parts: the k-th distance is larger relative to the box
+        if (MODE == 2 && radius * 1.001 < rho) rho = radius * 1.001;
+        bool staged = true;
+        for (int attempt = 0;; ++attempt) {
+            sg.rho = rho; sg.rho2 = rho * rho * (1.0 + 1e-12);
+            if (sg.stage()) break;
+            restage++;
+            if (len > 4 || attempt >= 6) { staged = false; break; }
+            rho *= 0.7;
+        }
+        if (!staged && len > 4) { len >>= 1; __syncwarp(); continue; }
+        parts++;
+        const int ncand = staged ? sg.n : 32;
+        candsum += ncand;
+        const int np = (ncand + KL_UNR - 1) & ~(KL_UNR - 1);
+        if (lane < np - ncand) sm.cand[ncand + lane] = make_float4(KF_BIG, KF_BIG, KF_BIG, __int_as_float(-1));
+        __syncwarp();
+        // error model of the staged FP32 coordinates: |coordinate| <= half home extent + rho
+        const float Lf = (float)((0.5 * hext + rho) * 1.001);
+        const float eA = 16.0f * KF_U * Lf, eC = 2.3e-13f * Lf * Lf;
+        const float rho1f = staged ? __double2float_rd(rho * rho * (1.0 - 1e-6)) : -1.0f;
+        float tcap = KF_TCAP;
+        if (MODE == 2) {
+            float r2f = __double2float_ru(r2d);
+            tcap = r2f * (1.0f + 1e-6f) + 2.0f * kf_err(r2f, eA, eC);
+            if (!(tcap < KF_TCAP)) staged = false;
+        }
+        KlAnswer A;
+        A.ok = false; A.cn = 0; A.why = 5; A.capf = __int_as_float(0x7f800000);
+        if (nq >= K && staged) A = kl_select<MODE>(sm, lane, np, K, qx, qy, qz, U, tcap, rho1f, eA, eC);
+        else if (nq >= K) A.capf = U + kf_err(U, eA, eC) * 1.0001f;
+        if (inpart && valid) {
+            capbuf[mypos] = A.ok ? -1.0f : A.capf;
+            if (out.stats) { n1 += A.why == 1; n2 += A.why == 2; n3 += A.why == 3; n4 += A.why == 4; n5 += A.why == 5; }
+            if (A.ok && out.nx) {
+                Cumul cu;
+                cu.clear();
+                for (int j = 0; j < A.cn; ++j) {
+                    int p = __float_as_int(sm.cand[sm.v.nb[j * 32 + lane]].w);
+                    double x = g.sx[p], y = g.sy[p], z = g.sz[p];
+                    if (MODE == 2 && !(dist2_rn(px, py, pz, x, y, z) < r2d)) continue;
+                    cu.add(x, y, z);
+                }
+                kf_store_normal(cu, g.sidx[mypos], out);
+            }
+        }
+        __syncwarp();
+        start += len;
+        len = start & -start;
+    }
+    if (out.stats) {
+        unsigned s1 = __reduce_add_sync(FULL, n1), s2 = __reduce_add_sync(FULL, n2), s3 = __reduce_add_sync(FULL, n3),
+                 s4 = __reduce_add_sync(FULL, n4), s5 = __reduce_add_sync(FULL, n5);
+        if (lane == 0) {
+            atomicAdd(out.stats + 16, 1ull);
+            atomicAdd(out.stats + 17, (unsigned long long)candsum);
+            atomicAdd(out.stats + 18, (unsigned long long)sg.scanned);
+            atomicAdd(out.stats + 19, (unsigned long long)s1);
+            atomicAdd(out.stats + 20, (unsigned long long)s2);
+            atomicAdd(out.stats + 21, (unsigned long long)s3);
+            atomicAdd(out.stats + 22, (unsigned long long)s4);
+            atomicAdd(out.stats + 23, (unsigned long long)s5);
+            atomicAdd(out.stats + 24, (unsigned long long)restage);
+            atomicAdd(out.stats + 25, (unsigned long long)parts);
+        }
+    }
+}
+
+
+// ---- tier 2: warp per failed query, exact FP64 range query within cap --------------------------------
+// A warp takes 32 consecutive entries of the compacted failure list.  For each it walks the range tables
+// with the fixed bound cap (lane = child box / lane = point, coalesced), appends every point with
+// d2 <= cap to a shared list, ranks the list by (d2, original index) and sums the cumulants of the K
+// smallest; the totals are parked in lane i, and at the end every lane finishes one query.
+#ifndef K2_WARPS
+#define K2_WARPS 4
+#endif
+#ifndef K2_SHRINK
+#define K2_SHRINK 0     // 1: a full list keeps its K smallest and lowers the bound; 0: the query goes to tier 3
+#endif
+#ifndef K2_LIST
+#define K2_LIST 128
+#endif
+
+struct K2WarpMem {
+    double d[K2_LIST], x[K2_LIST], y[K2_LIST], z[K2_LIST];
+    unsigned oidx[K2_LIST];
+};
+
+__device__ __forceinline__ double kl_box_lb(const GridDesc &g, int lvl, int64_t c, double qx, double qy, double qz)
+{
+    const double *b = g.box + g.off[lvl];
+    int64_t p = g.pitch[lvl];
+    double gx = fmax(fmax(__dsub_rn(b[c], qx), __dsub_rn(qx, b[3 * p + c])), 0.0);
+    double gy = fmax(fmax(__dsub_rn(b[p + c], qy), __dsub_rn(qy, b[4 * p + c])), 0.0);
+    double gz = fmax(fmax(__dsub_rn(b[2 * p + c], qz), __dsub_rn(qz, b[5 * p + c])), 0.0);
+    return __dadd_rn(__dadd_rn(__dmul_rn(gx, gx), __dmul_rn(gy, gy)), __dmul_rn(gz, gz));
+}
+
+template <int MODE>
+struct K2Range {
+    const GridDesc &g;
+    K2WarpMem &sm;
+    int lane;
+    double qx, qy, qz, cap, r2;
+    int cnt, K;
+    __device__ __forceinline__ K2Range(const GridDesc &g_, K2WarpMem &sm_) : g(g_), sm(sm_) {}
+
+    __device__ __forceinline__ void leaf(int64_t leaf_id)
+    {
+        int64_t p = leaf_id * 32 + lane;
+        bool hit = false;
+        double x = 0, y = 0, z = 0, d = 0;
+        if (p < g.n) {
+            x = g.sx[p]; y = g.sy[p]; z = g.sz[p];
+            d = dist2_rn(qx, qy, qz, x, y, z);
+            hit = d <= cap && (MODE != 2 || d < r2);
+        }
+        unsigned m = __ballot_sync(FULL, hit);
+        int at = cnt + __popc(m & ((1u << lane) - 1u));
+        if (hit && at < K2_LIST) { sm.d[at] = d; sm.x[at] = x; sm.y[at] = y; sm.z[at] = z; sm.oidx[at] = g.sidx[p]; }
+        cnt += __popc(m);
+        if (K2_SHRINK && cnt > K2_LIST - 32) shrink();
+    }
+
+    // the list is nearly full: keep its K smallest by (d2, original index) and lower the bound to the K-th
+    __device__ __forceinline__ void shrink()
+    {
+        __syncwarp();
+        constexpr int PER = K2_LIST / 32;
+        double de[PER], xe[PER], ye[PER], ze[PER];
+        unsigned oe[PER];
+        int rank[PER];
+#pragma unroll
+        for (int a = 0; a < PER; ++a) {
+            int e = a * 32 + lane;
+            bool ve = e < cnt;
+            de[a] = ve ? sm.d[e] : pos_inf(); oe[a] = ve ? sm.oidx[e] : 0xffffffffu;
+            xe[a] = ve ? sm.x[e] : 0.0; ye[a] = ve ? sm.y[e] : 0.0; ze[a] = ve ? sm.z[e] : 0.0;
+            rank[a] = 0;
+        }
+        for (int f = 0; f < cnt; ++f) {
+            double df = sm.d[f];
+            unsigned of = sm.oidx[f];
+#pragma unroll
+            for (int a = 0; a < PER; ++a) rank[a] += (df < de[a] || (df == de[a] && of < oe[a])) ? 1 : 0;
+        }
+        __syncwarp();
+        double kth = 0.0;
+#pragma unroll
+        for (int a = 0; a < PER; ++a) {
+            bool keep = a * 32 + lane < cnt && rank[a] < K;      // ranks are distinct: exactly K survive
+            if (keep) { int r = rank[a]; sm.d[r] = de[a]; sm.x[r] = xe[a]; sm.y[r] = ye[a]; sm.z[r] = ze[a]; sm.oidx[r] = oe[a]; }
+            if (keep && rank[a] == K - 1) kth = de[a];
+        }
+#pragma unroll
+        for (int dlt = 16; dlt > 0; dlt >>= 1) kth = fmax(kth, shfl_xor_d(kth, dlt));
+        cap = kth;
+        cnt = K;
+        __syncwarp();
     }
 
     template <int LVL>
@@ -81,12 +495,18 @@ struct KlStage {
     {
         int64_t c = parent * 32 + lane;
         bool ex = c < g.cnt[LVL];
-        double gp = ex ? gap(LVL, c) : pos_inf();
-        unsigned m = __ballot_sync(FULL, ex && gp <= rho2);
-        while (m && !overflow) {
-            int b = __ffs(m) - 1;
-            m &= m - 1;
-            if constexpr (LVL == 0) { if (parent * 32 + b != home) scan_group(parent * 32 + b); }
+        double lb = ex ? kl_box_lb(g, LVL, c, qx, qy, qz) : pos_inf();
+        unsigned m = __ballot_sync(FULL, ex && lb <= cap);
+        // nearest child first: the bound drops early (shrink) and the far children are never opened
+        const unsigned key = __float_as_uint(__double2float_rd(lb));
+        while (m && (K2_SHRINK || cnt <= K2_LIST)) {
+            m &= __ballot_sync(FULL, lb <= cap);      // the bound may have dropped
+            if (!m) break;
+            const bool mine = (m >> lane) & 1u;
+            const unsigned kmin = __reduce_min_sync(FULL, mine ? key : 0xffffffffu);
+            int b = __ffs(__ballot_sync(FULL, mine && key == kmin)) - 1;
+            m &= ~(1u << b);
+            if constexpr (LVL == 0) leaf(parent * 32 + b);
             else visit<LVL - 1>(parent * 32 + b);
         }
     }
@@ -104,269 +524,76 @@ struct KlStage {
     }
 };
 
-__device__ __forceinline__ float kl_d2(const float4 c, float qx, float qy, float qz)
-{
-    float dx = c.x - qx, dy = c.y - qy, dz = c.z - qz;
-    return fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-}
-
-// stats slots (out.stats, O3DPP_STATS=1): 16 warps, 17 candidates, 18 groups scanned, 19 fail-gap,
-// 20 fail-rho, 21 fail-boundary-overflow, 22 fail-count, 23 fail-warp (unstaged / short group), 24 restages
 template <int MODE>
-__global__ void __launch_bounds__(KL_WARPS * 32)
-knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, KnnOut out, float *__restrict__ capbuf)
-{
-    extern __shared__ __align__(16) unsigned char kl_smem[];
-    const int lane = lane_id(), w = threadIdx.x >> 5;
-    const int64_t leaf_id = (int64_t)blockIdx.x * KL_WARPS + w;
-    if (leaf_id >= g.cnt[0]) return;
-    KlWarpMem &sm = ((KlWarpMem *)kl_smem)[w];
-    const int64_t base = leaf_id * 32;
-    const int nq = (int)(g.n - base < 32 ? g.n - base : 32);
-    const int64_t mypos = base + lane;
-    const bool valid = lane < nq;
-    const double r2d = __dmul_rn(radius, radius);
-    double px = 0, py = 0, pz = 0;
-    if (valid) { px = g.sx[mypos]; py = g.sy[mypos]; pz = g.sz[mypos]; }
-
-    // ---- stage ---------------------------------------------------------------------------------
-    KlStage sg(g, sm);
-    sg.lane = lane; sg.scanned = 0; sg.home = leaf_id;
-    {
-        const double *b0 = g.box + g.off[0];
-        int64_t p0 = g.pitch[0];
-        sg.blo[0] = b0[leaf_id]; sg.blo[1] = b0[p0 + leaf_id]; sg.blo[2] = b0[2 * p0 + leaf_id];
-        sg.bhi[0] = b0[3 * p0 + leaf_id]; sg.bhi[1] = b0[4 * p0 + leaf_id]; sg.bhi[2] = b0[5 * p0 + leaf_id];
-    }
-    sg.cc[0] = 0.5 * (sg.blo[0] + sg.bhi[0]); sg.cc[1] = 0.5 * (sg.blo[1] + sg.bhi[1]); sg.cc[2] = 0.5 * (sg.blo[2] + sg.bhi[2]);
-    const double ex = sg.bhi[0] - sg.blo[0], ey = sg.bhi[1] - sg.blo[1], ez = sg.bhi[2] - sg.blo[2];
-    double rho = sqrt((ex * ex + ey * ey) + ez * ez) * (double)rho_scale;
-    if (MODE == 2 && radius * 1.001 < rho) rho = radius * 1.001;
-    // own query in local FP32; the home group occupies slots 0..31 (bit-identical to the query copies)
-    const float qx = valid ? (float)(px - sg.cc[0]) : KF_BIG, qy = valid ? (float)(py - sg.cc[1]) : KF_BIG,
-                qz = valid ? (float)(pz - sg.cc[2]) : KF_BIG;
-    sm.cand[lane] = make_float4(qx, qy, qz, __int_as_float(valid ? (int)mypos : -1));
-    bool staged = true;
-    unsigned restage = 0;
-    for (int attempt = 0;; ++attempt) {
-        sg.n = 32; sg.overflow = false; sg.rho = rho; sg.rho2 = rho * rho * (1.0 + 1e-12);
-        sg.walk();
-        if (!sg.overflow) break;
-        restage++;
-        if (attempt >= 8) { staged = false; sg.n = 32; break; }
-        rho *= 0.7;
-    }
-    const int ncand = sg.n;
-    const int np = (ncand + 3) & ~3;
-    if (lane < np - ncand) sm.cand[ncand + lane] = make_float4(KF_BIG, KF_BIG, KF_BIG, __int_as_float(-1));
-    __syncwarp();
-
-    // error model of the staged FP32 coordinates: |coordinate| <= half extent + rho
-    const float Lf = (float)((0.5 * fmax(fmax(ex, ey), ez) + rho) * 1.001);
-    const float eA = 16.0f * KF_U * Lf, eC = 2.3e-13f * Lf * Lf;
-    const float rho1f = staged ? __double2float_rd(rho * rho * (1.0 - 1e-6)) : -1.0f;
-    float tcap = KF_TCAP;
-    if (MODE == 2) {
-        float r2f = __double2float_ru(r2d);
-        tcap = r2f * (1.0f + 1e-6f) + 2.0f * kf_err(r2f, eA, eC);
-        if (!(tcap < KF_TCAP)) staged = false;
-    }
-
-    // ---- select: lane = query --------------------------------------------------------------------
-    const float4 *__restrict__ cd = sm.cand;
-    float U = 0.f;
-#pragma unroll 8
-    for (int s = 0; s < 32; ++s) {
-        float d = kl_d2(cd[s], qx, qy, qz);
-        if (s < nq) U = fmaxf(U, d);
-    }
-    bool ok = false;
-    float capf = __int_as_float(0x7f800000);
-    int cn = 0;
-    unsigned why = 0;     // 1 gap, 2 rho, 3 boundary overflow, 4 count, 5 warp
-    if (nq >= K && staged) {
-        float T = U;
-        bool capped = false;
-        if (MODE == 2 && tcap < T) { T = tcap; capped = true; }
-        const bool dead = !(T > 1e-36f);
-        const float scale = dead ? 0.f : (float)KL_NB / (T * 1.0001f);
-        unsigned *hist = sm.u.hist + lane;
-#pragma unroll
-        for (int b = 0; b < KL_NB; ++b) hist[b * 32] = 0u;
-        // pass B: histogram of d2 over [0, T]
-#pragma unroll 4
-        for (int s = 0; s < np; ++s) {
-            float d = kl_d2(cd[s], qx, qy, qz);
-            int b = __float2int_rz(d * scale);
-            if (b < KL_NB) hist[b * 32]++;
-        }
-        int c0 = 0, bstar = -1, cb = 0, acc = 0;
-#pragma unroll
-        for (int b = 0; b < KL_NB; ++b) {
-            int h = (int)hist[b * 32];
-            if (bstar < 0 && acc + h >= K) { bstar = b; c0 = acc; cb = h; }
-            acc += h;
-        }
-        const bool takeall = bstar < 0 && MODE == 2 && capped;   // fewer than K inside the radius
-        const bool counted = bstar >= 0;
-        if (takeall) bstar = KL_NB;
-        __syncwarp();     // the boundary lists alias the histograms of other lanes
-        // pass C: collect
-        int j = 0, mb = 0;
-        float bmin = KF_HUGE;
-        float *bd = sm.u.bnd.d + lane;
-        unsigned short *bs = sm.u.bnd.s + lane, *nbl = sm.nb + lane;
-#pragma unroll 4
-        for (int s = 0; s < np; ++s) {
-            float d = kl_d2(cd[s], qx, qy, qz);
-            int b = __float2int_rz(d * scale);
-            if (b < bstar) { if (j < 32) nbl[j * 32] = (unsigned short)s; j++; }
-            else if (b == bstar) { if (mb < KL_BND) { bd[mb * 32] = d; bs[mb * 32] = (unsigned short)s; } mb++; }
-            else bmin = fminf(bmin, d);
-        }
-        if (dead) { why = 4; capf = U + kf_err(U, eA, eC) * 1.0001f; }
-        else if (takeall) {
-            ok = tcap + kf_err(tcap, eA, eC) <= rho1f && j <= 32;
-            capf = tcap;
-            if (!ok) why = 2;
-        } else if (!counted) { why = 4; capf = U + kf_err(U, eA, eC) * 1.0001f; }
-        else if (cb > KL_BND) {
-            why = 3;
-            float edge = (float)(bstar + 1) / scale * 1.001f;
-            capf = edge + kf_err(edge, eA, eC) * 1.0001f;
-        } else {
-            const int need = K - c0;
-            float a = 0.f;
-            for (int r = 0; r < need; ++r) {
-                float best = KF_HUGE;
-                int be = 0;
-                for (int e = 0; e < cb; ++e) { float v = bd[e * 32]; if (v < best) { best = v; be = e; } }
-                a = best;
-                if (j < 32) nbl[j * 32] = bs[be * 32];
-                j++;
-                bd[be * 32] = KF_HUGE;
-            }
-            float rest = bmin;
-            for (int e = 0; e < cb; ++e) rest = fminf(rest, bd[e * 32]);
-            const float ea = kf_err(a, eA, eC);
-            const bool c1 = rest - a > 2.0f * kf_err(rest, eA, eC), c2 = a + ea <= rho1f;
-            ok = c1 && c2;
-            capf = a + ea * 1.0001f;
-            if (!c1) why = 1; else if (!c2) why = 2;
-        }
-        cn = j;
-    } else {
-        why = 5;
-        if (nq >= K) capf = U + kf_err(U, eA, eC) * 1.0001f;
-    }
-    if (valid) capbuf[mypos] = ok ? -1.0f : capf;
-    if (out.stats) {
-        unsigned m1 = __ballot_sync(FULL, valid && why == 1), m2 = __ballot_sync(FULL, valid && why == 2), m3 = __ballot_sync(FULL, valid && why == 3),
-                 m4 = __ballot_sync(FULL, valid && why == 4), m5 = __ballot_sync(FULL, valid && why == 5);
-        if (lane == 0) {
-            atomicAdd(out.stats + 16, 1ull);
-            atomicAdd(out.stats + 17, (unsigned long long)ncand);
-            atomicAdd(out.stats + 18, (unsigned long long)sg.scanned);
-            atomicAdd(out.stats + 19, (unsigned long long)__popc(m1));
-            atomicAdd(out.stats + 20, (unsigned long long)__popc(m2));
-            atomicAdd(out.stats + 21, (unsigned long long)__popc(m3));
-            atomicAdd(out.stats + 22, (unsigned long long)__popc(m4));
-            atomicAdd(out.stats + 23, (unsigned long long)__popc(m5));
-            atomicAdd(out.stats + 24, (unsigned long long)restage);
-        }
-    }
-    // ---- finish ------------------------------------------------------------------------------------
-    if (!valid || !ok || !out.nx) return;
-    Cumul cu;
-    cu.clear();
-    for (int j = 0; j < cn; ++j) {
-        int p = __float_as_int(cd[sm.nb[j * 32 + lane]].w);
-        double x = g.sx[p], y = g.sy[p], z = g.sz[p];
-        if (MODE == 2 && !(dist2_rn(px, py, pz, x, y, z) < r2d)) continue;
-        cu.add(x, y, z);
-    }
-    kf_store_normal(cu, g.sidx[mypos], out);
-}
-
-// ---- tier 2: thread per failed query, exact FP64 range query within cap -----------------------------
-#define K2_THREADS 64
-#define K2_LIST 64
-
-__device__ __forceinline__ double kl_box_lb(const GridDesc &g, int lvl, int64_t c, double qx, double qy, double qz)
-{
-    const double *b = g.box + g.off[lvl];
-    int64_t p = g.pitch[lvl];
-    double gx = fmax(fmax(__dsub_rn(b[c], qx), __dsub_rn(qx, b[3 * p + c])), 0.0);
-    double gy = fmax(fmax(__dsub_rn(b[p + c], qy), __dsub_rn(qy, b[4 * p + c])), 0.0);
-    double gz = fmax(fmax(__dsub_rn(b[2 * p + c], qz), __dsub_rn(qz, b[5 * p + c])), 0.0);
-    return __dadd_rn(__dadd_rn(__dmul_rn(gx, gx), __dmul_rn(gy, gy)), __dmul_rn(gz, gz));
-}
-
-template <int MODE>
-__global__ void __launch_bounds__(K2_THREADS)
+__global__ void __launch_bounds__(K2_WARPS * 32)
 knn_range_kernel(const GridDesc g, int K, double radius, KnnOut out, const int32_t *__restrict__ list, int m,
                  float *__restrict__ capbuf)
 {
-    extern __shared__ __align__(16) unsigned char k2_smem[];
-    double *ld = (double *)k2_smem + threadIdx.x;                              // [entry][thread]
-    int *lp = (int *)((double *)k2_smem + K2_LIST * K2_THREADS) + threadIdx.x;
-    const int t = blockIdx.x * K2_THREADS + threadIdx.x;
-    if (t >= m) return;
-    const int q = list[t];
-    const float capf = capbuf[q];
-    if (!(capf < 3.0e38f)) return;          // no bound known: the exact search (tier 3) takes it
-    const double qx = g.sx[q], qy = g.sy[q], qz = g.sz[q];
-    const double r2 = __dmul_rn(radius, radius);
-    double cap = (double)capf;
-    if (MODE == 2 && r2 < cap) cap = r2;
-    int cnt = 0;
-    int lvl = g.levels - 1;
-    int64_t node[KNN_MAX_LEVELS];
-    int ch[KNN_MAX_LEVELS];
-    node[lvl] = 0; ch[lvl] = 0;
-    while (lvl < g.levels) {
-        const int k = ch[lvl];
-        const int64_t c = node[lvl] * 32 + k;
-        if (k >= 32 || c >= g.cnt[lvl]) { ++lvl; continue; }
-        ch[lvl] = k + 1;
-        if (kl_box_lb(g, lvl, c, qx, qy, qz) > cap) continue;
-        if (lvl > 0) { --lvl; node[lvl] = c; ch[lvl] = 0; continue; }
-        const int64_t p0 = c * 32;
-        const int e = (int)(g.n - p0 < 32 ? g.n - p0 : 32);
-        for (int j = 0; j < e; ++j) {
-            double d = dist2_rn(qx, qy, qz, g.sx[p0 + j], g.sy[p0 + j], g.sz[p0 + j]);
-            if (d <= cap && (MODE != 2 || d < r2)) {
-                if (cnt < K2_LIST) { ld[cnt * K2_THREADS] = d; lp[cnt * K2_THREADS] = (int)(p0 + j); }
-                cnt++;
-            }
+    __shared__ K2WarpMem k2_sm[K2_WARPS];
+    const int lane = lane_id(), w = threadIdx.x >> 5;
+    const int64_t first = ((int64_t)blockIdx.x * K2_WARPS + w) * 32;
+    if (first >= m) return;
+    const int nq = (int)(m - first < 32 ? m - first : 32);
+    K2WarpMem &sm = k2_sm[w];
+    // lane i owns query i of the batch
+    int myq = -1;
+    double mx = 0, my = 0, mz = 0, mycap = pos_inf();
+    if (lane < nq) {
+        myq = list[first + lane];
+        mx = g.sx[myq]; my = g.sy[myq]; mz = g.sz[myq];
+        float cf = capbuf[myq];
+        if (cf < 3.0e38f) mycap = (double)cf;
+    }
+    K2Range<MODE> rq(g, sm);
+    rq.lane = lane; rq.K = K;
+    rq.r2 = __dmul_rn(radius, radius);
+    Cumul mine;
+    mine.clear();
+    bool done = false;
+    for (int i = 0; i < nq; ++i) {
+        double cap = shfl_d(mycap, i);
+        if (!(cap < 1e300)) continue;            // no bound known: the exact search (tier 3) takes it
+        if (MODE == 2 && rq.r2 < cap) cap = rq.r2;
+        rq.cap = cap;
+        rq.qx = shfl_d(mx, i); rq.qy = shfl_d(my, i); rq.qz = shfl_d(mz, i);
+        rq.cnt = 0;
+        rq.walk();
+        const int cnt = rq.cnt;
+        if (cnt > K2_LIST) continue;             // (K2_SHRINK == 0) too many candidates inside the bound: tier 3
+        __syncwarp();
+        // rank by (d2, original index); the K smallest contribute
+        Cumul cu;
+        cu.clear();
+        for (int e0 = 0; e0 < cnt; e0 += 32) {
+            const int e = e0 + lane;
+            const bool ve = e < cnt;
+            const double de = ve ? sm.d[e] : 0.0;
+            const unsigned oe = ve ? sm.oidx[e] : 0u;
+            int rank = 0;
+            if (cnt > K)
+                for (int f = 0; f < cnt; ++f) {
+                    double df = sm.d[f];
+                    unsigned of = sm.oidx[f];
+                    rank += (df < de || (df == de && of < oe)) ? 1 : 0;
+                }
+            if (ve && rank < K) cu.add(sm.x[e], sm.y[e], sm.z[e]);
         }
-        if (cnt > K2_LIST) break;
-    }
-    if (cnt > K2_LIST) return;              // too many candidates inside the bound: tier 3
-    // keep the K smallest by (d2, original index): drop the largest until K remain
-    int mc = cnt;
-    while (mc > K) {
-        double bd = ld[0];
-        int be = 0, bp = lp[0];
-        for (int e = 1; e < mc; ++e) {
-            double d = ld[e * K2_THREADS];
-            int p = lp[e * K2_THREADS];
-            if (d > bd || (d == bd && g.sidx[p] > g.sidx[bp])) { bd = d; be = e; bp = p; }
+#pragma unroll
+        for (int a = 0; a < 9; ++a) {
+            double v = cu.c[a];
+#pragma unroll
+            for (int dlt = 16; dlt > 0; dlt >>= 1) v += shfl_xor_d(v, dlt);
+            if (lane == i) mine.c[a] = v;
         }
-        --mc;
-        ld[be * K2_THREADS] = ld[mc * K2_THREADS];
-        lp[be * K2_THREADS] = lp[mc * K2_THREADS];
+        int tn = __reduce_add_sync(FULL, cu.n);
+        if (lane == i) { mine.n = tn; done = true; }
+        __syncwarp();
     }
-    capbuf[q] = -1.0f;
-    if (!out.nx) return;
-    Cumul cu;
-    cu.clear();
-    for (int e = 0; e < mc; ++e) {
-        int p = lp[e * K2_THREADS];
-        cu.add(g.sx[p], g.sy[p], g.sz[p]);
-    }
-    kf_store_normal(cu, g.sidx[q], out);
+    if (!done) return;
+    capbuf[myq] = -1.0f;
+    if (out.nx) kf_store_normal(mine, g.sidx[myq], out);
 }
+
 
 // ---- tier 3: warp per query, exact FP64 list search -------------------------------------------------
 template <int MODE>

@@ -12,7 +12,7 @@ import numpy as np
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_PKG)
-LIB_PATH = os.path.join(_ROOT, "libo3dpp_b200.so")
+LIB_PATH = os.environ.get("O3DPP_LIB") or os.path.join(_ROOT, "libo3dpp_b200.so")   # O3DPP_LIB: tuning builds
 
 ATTR_POINTS, ATTR_NORMALS, ATTR_COLORS = 0, 1, 2
 SEARCH_KNN, SEARCH_RADIUS, SEARCH_HYBRID = 0, 1, 2
