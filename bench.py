@@ -179,6 +179,7 @@ def main():
         e[3].synchronize()
         stages.append({"voxel": e[0].elapsed_time(e[1]), "normals": e[1].elapsed_time(e[2]),
                        "segment": e[2].elapsed_time(e[3]), "grid_build": tk[0], "knn_kernel": tk[1],
+                       "knn_tier1": tk[2], "knn_tier2": tk[3], "knn_tier3": tk[6], "tier2_queries": tk[4], "tier3_queries": tk[5],
                        "ransac_score": ts[1], "ransac_scored": ts[7], "V": V})
         return plane
 
@@ -240,7 +241,8 @@ def main():
             "e2e": {"value": world * N / (t_e2e * 1e-3) / 1e6, "unit": "Mpoints/s", "ms_per_step": t_e2e,
                     "h2d_bytes_per_step": 24 * N, "d2h_bytes_per_step": 24 * N + 4 * n_inl + 32},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "knn_normals_kernel", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "hbm", "kernel": "knn_lane_kernel (tier 1) + knn_range_kernel + knn_exact_kernel: the whole neighbour search of one "
+                                                        "estimate_normals call, tiers 2 and 3 included in kernel_ms", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": ALGO_BYTES_PER_POINT_KNN * N, "kernel_ms": knn_ms},
             "clocks": clocks,

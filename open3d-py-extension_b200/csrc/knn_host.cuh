@@ -153,9 +153,10 @@ static int search_impl(o3dpp_ctx *c, int mode, int K, double radius, bool want_n
         if (c->want_stats && c->stats[16]) {
             double nq = (double)n, nw = (double)c->stats[16];
             fprintf(stderr, "[o3dpp lane] n=%lld mode=%d K=%d tier1 %.3f ms, tier2 %.3f ms, tier3 %.3f ms (tier2 %lld, tier3 %lld queries) | per warp: parts %.3f candidates %.1f "
-                    "groups-scanned %.1f restages %.3f | fail per query: gap %.4f rho %.4f boundary %.4f count %.4f warp %.4f\n", (long long)n, mode, K,
+                    "groups-scanned %.1f restages %.3f | fail per query: gap %.4f rho %.4f boundary %.4f count %.4f warp %.4f | split warps %.3f, kcycles per warp: single %.1f split %.1f\n", (long long)n, mode, K,
                     t1, t2, t3, (long long)c->timings[4], (long long)c->timings[5], c->stats[25] / nw, c->stats[17] / nw, c->stats[18] / nw, c->stats[24] / nw,
-                    c->stats[19] / nq, c->stats[20] / nq, c->stats[21] / nq, c->stats[22] / nq, c->stats[23] / nq);
+                    c->stats[19] / nq, c->stats[20] / nq, c->stats[21] / nq, c->stats[22] / nq, c->stats[23] / nq,
+                    c->stats[28] / nw, c->stats[26] / (nw - c->stats[28] + 1e-9) / 1e3, c->stats[27] / (c->stats[28] + 1e-9) / 1e3);
         }
     }
     if (c->want_stats) {

@@ -39,6 +39,9 @@
 #ifndef KL_UNR
 #define KL_UNR 4       // candidates per iteration of the two select passes
 #endif
+#ifndef KL_ATOM
+#define KL_ATOM 1       // histogram update: 1 = shared atomic (fire and forget), 0 = load/add/store
+#endif
 #ifndef KL_MINB
 #define KL_MINB 12
 #endif
@@ -47,6 +50,8 @@
 #endif
 
 struct KlWarpMem {
+    // candidates, two to a 32-byte record {x0 x1 y0 y1 | z0 z1 p0 p1} so that the select passes run on packed
+    // FP32 pairs (FFMA2); p = sorted position bits
     float4 cand[KL_CAP + 8];
     union {
         unsigned hist[(KL_NB + 1) * 32];                                        // [bin][lane]
@@ -57,6 +62,25 @@ struct KlWarpMem {
         unsigned gl[KL_GMAX];                                                // cell groups to scan (stage only)
     } v;
 };
+
+
+// candidate s lives in half (s & 1) of record s >> 1
+__device__ __forceinline__ void kl_put(float4 *cand, int s, float x, float y, float z, int pos)
+{
+    float *r = (float *)(cand + (s & ~1)) + (s & 1);
+    r[0] = x; r[2] = y; r[4] = z; r[6] = __int_as_float(pos);
+}
+__device__ __forceinline__ int kl_pos(const float4 *cand, int s)
+{
+    return __float_as_int(((const float *)(cand + (s & ~1)))[6 + (s & 1)]);
+}
+// d2 of the two candidates of record {a, b} to the query (nq* = the negated query coordinate, twice)
+__device__ __forceinline__ float2 kl_d2pair(const float4 a, const float4 b, float2 nqx, float2 nqy, float2 nqz)
+{
+    float2 dx = __fadd2_rn(make_float2(a.x, a.y), nqx), dy = __fadd2_rn(make_float2(a.z, a.w), nqy),
+           dz = __fadd2_rn(make_float2(b.x, b.y), nqz);
+    return __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
+}
 
 struct KlStage {
     const GridDesc &g;
@@ -108,8 +132,7 @@ struct KlStage {
                   z >= blo[2] - rho && z <= bhi[2] + rho;
         unsigned m = __ballot_sync(FULL, in);
         int at = n + __popc(m & ((1u << lane) - 1u));
-        if (in && at < KL_CAP)
-            sm.cand[at] = make_float4((float)(x - cc[0]), (float)(y - cc[1]), (float)(z - cc[2]), __int_as_float((int)p));
+        if (in && at < KL_CAP) kl_put(sm.cand, at, (float)(x - cc[0]), (float)(y - cc[1]), (float)(z - cc[2]), (int)p);
         n += __popc(m);
     }
 
@@ -148,11 +171,6 @@ struct KlStage {
     }
 };
 
-__device__ __forceinline__ float kl_d2(const float4 c, float qx, float qy, float qz)
-{
-    float dx = c.x - qx, dy = c.y - qy, dz = c.z - qz;
-    return fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-}
 
 // quarter-octave bin of a non-negative float relative to `base` (the bits of d2 >> 21 keep the exponent and
 // two mantissa bits): monotone in d2, three integer instructions
@@ -188,15 +206,22 @@ __device__ __forceinline__ KlAnswer kl_select(KlWarpMem &sm, int lane, int np, i
 #pragma unroll
     for (int b = 0; b < KL_NB; ++b) hist[b * 32] = 0u;
     // pass B: lane-private histogram of d2 (candidates are broadcast reads, loads issued ahead of the updates)
+    const float2 nqx = make_float2(-qx, -qx), nqy = make_float2(-qy, -qy), nqz = make_float2(-qz, -qz);
     for (int s = 0; s < np; s += KL_UNR) {
         float4 cc[KL_UNR];
         int bb[KL_UNR];
 #pragma unroll
         for (int u = 0; u < KL_UNR; ++u) cc[u] = cd[s + u];
 #pragma unroll
-        for (int u = 0; u < KL_UNR; ++u) bb[u] = kl_bin(kl_d2(cc[u], qx, qy, qz), base);
+        for (int u = 0; u < KL_UNR; u += 2) {
+            float2 d = kl_d2pair(cc[u], cc[u + 1], nqx, nqy, nqz);
+            bb[u] = kl_bin(d.x, base); bb[u + 1] = kl_bin(d.y, base);
+        }
 #pragma unroll
-        for (int u = 0; u < KL_UNR; ++u) atomicAdd(hist + bb[u] * 32, 1u);
+        for (int u = 0; u < KL_UNR; ++u) {
+            if (KL_ATOM) atomicAdd(hist + bb[u] * 32, 1u);
+            else hist[bb[u] * 32]++;
+        }
     }
     int c0 = 0, bstar = -1, cb = 0, acc = 0;
 #pragma unroll
@@ -222,7 +247,11 @@ __device__ __forceinline__ KlAnswer kl_select(KlWarpMem &sm, int lane, int np, i
 #pragma unroll
         for (int u = 0; u < KL_UNR; ++u) cc[u] = cd[s + u];
 #pragma unroll
-        for (int u = 0; u < KL_UNR; ++u) { dd[u] = kl_d2(cc[u], qx, qy, qz); bb[u] = kl_bin(dd[u], base); }
+        for (int u = 0; u < KL_UNR; u += 2) {
+            float2 d = kl_d2pair(cc[u], cc[u + 1], nqx, nqy, nqz);
+            dd[u] = d.x; dd[u + 1] = d.y;
+            bb[u] = kl_bin(d.x, base); bb[u + 1] = kl_bin(d.y, base);
+        }
 #pragma unroll
         for (int u = 0; u < KL_UNR; ++u) {
             if (bb[u] < bstar) { *nbp = (unsigned short)(s + u); nbp += 32; }
@@ -285,6 +314,7 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, KnnOut 
     double px = 0, py = 0, pz = 0;
     if (valid) { px = g.sx[mypos]; py = g.sy[mypos]; pz = g.sz[mypos]; }
 
+    const long long t_start = out.stats ? clock64() : 0;
     KlStage sg(g, sm);
     sg.lane = lane; sg.scanned = 0; sg.home = leaf_id;
     // the home box; candidate coordinates are relative to its centre for every part of the group
@@ -300,14 +330,18 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, KnnOut 
     // own query in local FP32; the home group occupies slots 0..31 (bit-identical to the query copies)
     const float qx = valid ? (float)(px - sg.cc[0]) : KF_BIG, qy = valid ? (float)(py - sg.cc[1]) : KF_BIG,
                 qz = valid ? (float)(pz - sg.cc[2]) : KF_BIG;
-    sm.cand[lane] = make_float4(qx, qy, qz, __int_as_float(valid ? (int)mypos : -1));
+    kl_put(sm.cand, lane, qx, qy, qz, valid ? (int)mypos : -1);
     __syncwarp();
     // U = largest d2 to a member of the home group: bounds the k-th d2 when the group holds >= K points
     float U = 0.f;
+    {
+        const float2 nqx = make_float2(-qx, -qx), nqy = make_float2(-qy, -qy), nqz = make_float2(-qz, -qz);
 #pragma unroll 8
-    for (int s = 0; s < 32; ++s) {
-        float d = kl_d2(sm.cand[s], qx, qy, qz);
-        if (s < nq) U = fmaxf(U, d);
+        for (int s = 0; s < 32; s += 2) {
+            float2 d = kl_d2pair(sm.cand[s], sm.cand[s + 1], nqx, nqy, nqz);
+            if (s < nq) U = fmaxf(U, d.x);
+            if (s + 1 < nq) U = fmaxf(U, d.y);
+        }
     }
     unsigned restage = 0, parts = 0, candsum = 0;
     unsigned n1 = 0, n2 = 0, n3 = 0, n4 = 0, n5 = 0;
@@ -343,7 +377,7 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, KnnOut 
         const int ncand = staged ? sg.n : 32;
         candsum += ncand;
         const int np = (ncand + KL_UNR - 1) & ~(KL_UNR - 1);
-        if (lane < np - ncand) sm.cand[ncand + lane] = make_float4(KF_BIG, KF_BIG, KF_BIG, __int_as_float(-1));
+        if (lane < np - ncand) kl_put(sm.cand, ncand + lane, KF_BIG, KF_BIG, KF_BIG, -1);
         __syncwarp();
         // error model of the staged FP32 coordinates: |coordinate| <= half home extent + rho
         const float Lf = (float)((0.5 * hext + rho) * 1.001);
@@ -366,7 +400,7 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, KnnOut 
                 Cumul cu;
                 cu.clear();
                 for (int j = 0; j < A.cn; ++j) {
-                    int p = __float_as_int(sm.cand[sm.v.nb[j * 32 + lane]].w);
+                    int p = kl_pos(sm.cand, sm.v.nb[j * 32 + lane]);
                     double x = g.sx[p], y = g.sy[p], z = g.sz[p];
                     if (MODE == 2 && !(dist2_rn(px, py, pz, x, y, z) < r2d)) continue;
                     cu.add(x, y, z);
@@ -392,6 +426,8 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, KnnOut 
             atomicAdd(out.stats + 23, (unsigned long long)s5);
             atomicAdd(out.stats + 24, (unsigned long long)restage);
             atomicAdd(out.stats + 25, (unsigned long long)parts);
+            atomicAdd(out.stats + (parts > 1 ? 27 : 26), (unsigned long long)(clock64() - t_start));
+            if (parts > 1) atomicAdd(out.stats + 28, 1ull);
         }
     }
 }
