@@ -154,6 +154,25 @@ O3DPP_API int o3dpp_select(o3dpp_ctx *ctx, const int32_t *idx, int64_t m, int in
 /* same with the last segment_plane's inlier list, without a host round trip */
 O3DPP_API int o3dpp_select_inliers(o3dpp_ctx *ctx, int invert);
 
+/* ---- a scan sharded across GPUs by spatial slab (the reference has no counterpart: it runs
+ *      pcd.segment_plane / pcd.estimate_normals, PointCloud.py:68-77, on one host).  These are the steps of
+ *      o3dpp_segment_plane as separate calls, so that the host side can all-reduce between them:
+ *      sample -> (owners publish the sampled points) -> planes -> score on every rank -> all-reduce ->
+ *      host replay of the selection -> inliers + coordinate sums per rank -> all-reduce -> moments -> all-reduce.
+ *      n_use > 0 restricts a call to the first n_use points of the cloud (owned points first, halo after). */
+O3DPP_API int o3dpp_sample_philox(o3dpp_ctx *ctx, uint64_t seed, int64_t n, int ransac_n, int num_iterations,
+                                  int64_t *out);
+O3DPP_API int o3dpp_planes_from_points(o3dpp_ctx *ctx, const double *pts, int ransac_n, int num_iterations,
+                                       double *planes);
+O3DPP_API int o3dpp_score_planes(o3dpp_ctx *ctx, const double *planes, int num_planes, double distance_threshold,
+                                 int64_t n_use, int64_t *counts, double *errs);
+O3DPP_API int o3dpp_plane_inliers(o3dpp_ctx *ctx, const double *plane4, double distance_threshold, int64_t n_use,
+                                  int64_t *n_inliers, double *sum3);
+O3DPP_API int o3dpp_inlier_moments(o3dpp_ctx *ctx, const double *centroid3, double *mom6);
+/* per point, an upper bound of the squared distance to its k-th neighbour left by the last
+ * o3dpp_estimate_normals (knn <= 32, KNN or hybrid): tells which queries near a slab cut need a wider halo */
+O3DPP_API int o3dpp_fetch_kth_bound(o3dpp_ctx *ctx, float *out);
+
 #ifdef __cplusplus
 }
 #endif

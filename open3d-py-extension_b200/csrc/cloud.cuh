@@ -70,6 +70,7 @@ static int attr_alloc(Attr3 *a, int64_t n)
 static void invalidate_derived(o3dpp_ctx *c)
 {
     c->vox_valid = false;
+    c->kth_valid = false;
     c->r_ninl = -1;
 }
 

@@ -96,6 +96,7 @@ struct o3dpp_ctx {
 
     // voxel results (device resident until the next voxel()/upload)
     bool vox_valid = false;
+    bool kth_valid = false;               // g_ncnt holds the per-query k-th distance bounds of the last estimate_normals
     int64_t vox_V = 0, vox_n = 0;
     DevBuf v_order, v_seg, v_oct, v_rep, v_rep_asc, v_count, v_centroid, v_normal, v_color, v_cubic;
 

@@ -145,7 +145,7 @@ __device__ __forceinline__ void kf_store_normal(const Cumul &cu, uint32_t qo, co
 // cap = a known upper bound of the k-th d2 (+inf if none)
 template <int MODE>
 __device__ __noinline__ void kf_slow_query(const GridDesc &g, int64_t leaf_id, int i, int K, double r2, double cap,
-                                           const KnnOut &out)
+                                           const KnnOut &out, float *kth_out = nullptr)
 {
     const int lane = lane_id();
     const int64_t mypos = leaf_id * 32 + lane;
@@ -164,6 +164,10 @@ __device__ __noinline__ void kf_slow_query(const GridDesc &g, int64_t leaf_id, i
     st.walk();
     bool ok = lane < K && st.L.pos[0] >= 0 && (MODE != 2 || st.L.d2[0] < r2);
     int c = __popc(__ballot_sync(FULL, ok));
+    if (kth_out) {      // the exact k-th d2 (rounded up), negated: "answered" in the lane path's bound buffer
+        double kd = shfl_d(st.L.d2[0], c > 0 ? c - 1 : 0);
+        if (lane == 0) *kth_out = -fmaxf(c > 0 ? __double2float_ru(kd) : 0.f, 1e-30f);
+    }
     if (!out.nx) return;
     Cumul cu;
     cu.clear();

@@ -61,6 +61,7 @@ static int launch_lane(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, c
     } else cudaEventRecord(c->ev[5], c->stream);
     c->timings[4] = (double)m2;
     c->timings[5] = (double)m3;
+    c->kth_valid = true;
     return 0;
 }
 
@@ -114,6 +115,7 @@ static int search_impl(o3dpp_ctx *c, int mode, int K, double radius, bool want_n
         CU_TRY(cudaMemsetAsync(out.stats, 0, 256, c->stream));
     }
     GridDesc gd;
+    c->kth_valid = false;
     cudaEventRecord(c->ev[0], c->stream);
     O3_TRY(grid_build(c, &gd));
     cudaEventRecord(c->ev[1], c->stream);
@@ -166,5 +168,29 @@ static int search_impl(o3dpp_ctx *c, int mode, int K, double radius, bool want_n
                 c->stats[4] / nq, c->stats[6] / nq, c->stats[7] / nq, c->stats[8] / nq, c->stats[9] / nq, c->stats[10] / nq,
                 c->stats[11] / nq, c->stats[12] / nq, c->stats[14] / nq, c->stats[15] / nq, c->stats[5] / nw, c->stats[13] / nw);
     }
+    return 0;
+}
+
+
+// per point (original index): an upper bound of the squared distance to its k-th neighbour, as left by
+// the lane path of the last estimate_normals (exact for queries answered by tiers 2 and 3).  The slab-sharded
+// KNN uses it to tell which queries near a cut need a wider halo (open3dpypro/sharding.py).
+__global__ void kth_scatter_kernel(const float *__restrict__ capbuf, const uint32_t *__restrict__ sidx, int64_t n, float *__restrict__ out)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        float v = capbuf[i];
+        out[sidx[i]] = v < 0.f ? -v : __int_as_float(0x7f800000);
+    }
+}
+
+static int fetch_kth_impl(o3dpp_ctx *c, float *host)
+{
+    if (!c->kth_valid) return set_err(O3DPP_E_STATE, "no k-th distance bounds: run o3dpp_estimate_normals (knn <= 32, KNN or hybrid) first");
+    int64_t n = c->n;
+    O3_TRY(c->g_nd2.ensure((size_t)n * 4 + 64));
+    LAUNCH(c, kth_scatter_kernel, grid_for(c, n, 256, 16), 256, 0, c->g_ncnt.as<float>(), c->g_sidx.as<uint32_t>(), n, c->g_nd2.as<float>());
+    O3_TRY(check_launch("kth_scatter"));
+    O3_TRY(d2h(c, host, c->g_nd2.p, (size_t)n * 4));
+    CU_TRY(cudaStreamSynchronize(c->stream));
     return 0;
 }

@@ -394,7 +394,7 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, KnnOut 
         if (nq >= K && staged) A = kl_select<MODE>(sm, lane, np, K, qx, qy, qz, U, tcap, rho1f, eA, eC);
         else if (nq >= K) A.capf = U + kf_err(U, eA, eC) * 1.0001f;
         if (inpart && valid) {
-            capbuf[mypos] = A.ok ? -1.0f : A.capf;
+            capbuf[mypos] = A.ok ? -fmaxf(A.capf, 1e-30f) : A.capf;   // negative = answered, magnitude bounds the k-th d2
             if (out.stats) { n1 += A.why == 1; n2 += A.why == 2; n3 += A.why == 3; n4 += A.why == 4; n5 += A.why == 5; }
             if (A.ok && out.nx) {
                 Cumul cu;
@@ -586,6 +586,7 @@ knn_range_kernel(const GridDesc g, int K, double radius, KnnOut out, const int32
     Cumul mine;
     mine.clear();
     bool done = false;
+    double mykth = 0.0;
     for (int i = 0; i < nq; ++i) {
         double cap = shfl_d(mycap, i);
         if (!(cap < 1e300)) continue;            // no bound known: the exact search (tier 3) takes it
@@ -600,6 +601,7 @@ knn_range_kernel(const GridDesc g, int K, double radius, KnnOut out, const int32
         // rank by (d2, original index); the K smallest contribute
         Cumul cu;
         cu.clear();
+        double kd = 0.0;
         for (int e0 = 0; e0 < cnt; e0 += 32) {
             const int e = e0 + lane;
             const bool ve = e < cnt;
@@ -612,8 +614,11 @@ knn_range_kernel(const GridDesc g, int K, double radius, KnnOut out, const int32
                     unsigned of = sm.oidx[f];
                     rank += (df < de || (df == de && of < oe)) ? 1 : 0;
                 }
-            if (ve && rank < K) cu.add(sm.x[e], sm.y[e], sm.z[e]);
+            if (ve && rank < K) { cu.add(sm.x[e], sm.y[e], sm.z[e]); kd = fmax(kd, de); }
         }
+#pragma unroll
+        for (int dlt = 16; dlt > 0; dlt >>= 1) kd = fmax(kd, shfl_xor_d(kd, dlt));
+        if (lane == i) mykth = kd;
 #pragma unroll
         for (int a = 0; a < 9; ++a) {
             double v = cu.c[a];
@@ -626,7 +631,7 @@ knn_range_kernel(const GridDesc g, int K, double radius, KnnOut out, const int32
         __syncwarp();
     }
     if (!done) return;
-    capbuf[myq] = -1.0f;
+    capbuf[myq] = -fmaxf(__double2float_ru(mykth), 1e-30f);
     if (out.nx) kf_store_normal(mine, g.sidx[myq], out);
 }
 
@@ -635,12 +640,12 @@ knn_range_kernel(const GridDesc g, int K, double radius, KnnOut out, const int32
 template <int MODE>
 __global__ void __launch_bounds__(128)
 knn_exact_kernel(const GridDesc g, int K, double radius, KnnOut out, const int32_t *__restrict__ list, int m,
-                 const float *__restrict__ capbuf)
+                 float *__restrict__ capbuf)
 {
     const int w = blockIdx.x * 4 + (threadIdx.x >> 5);
     if (w >= m) return;
     const int q = list[w];
     const float capf = capbuf[q];
     const double cap = capf < 3.0e38f ? (double)capf : pos_inf();
-    kf_slow_query<MODE>(g, (int64_t)(q >> 5), q & 31, K, __dmul_rn(radius, radius), cap, out);
+    kf_slow_query<MODE>(g, (int64_t)(q >> 5), q & 31, K, __dmul_rn(radius, radius), cap, out, capbuf + q);
 }

@@ -2,7 +2,7 @@
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -fmad=false
 //        -Xcompiler -fPIC,-ffp-contract=off,-fvisibility=hidden -shared -o libo3dpp_b200.so o3dpp.cu
 // There is no CPU path in this library: every entry point needs a live CUDA context.
-#include "ransac.cuh"
+#include "ransac_parts.cuh"
 #include <stdlib.h>
 
 #define CTX_CHECK(c)                                                      \
@@ -287,3 +287,43 @@ O3DPP_API int o3dpp_select_inliers(o3dpp_ctx *c, int invert)
 }
 
 }  // extern "C"
+
+/* ---- slab-sharded scans: the pieces of segment_plane and the k-th distance bounds ------------------- */
+O3DPP_API int o3dpp_sample_philox(o3dpp_ctx *c, uint64_t seed, int64_t n, int ransac_n, int num_iterations, int64_t *out)
+{
+    CTX_CHECK(c);
+    if (!out) return set_err(O3DPP_E_ARG, "null argument");
+    return sample_philox_impl(c, seed, n, ransac_n, num_iterations, out);
+}
+O3DPP_API int o3dpp_planes_from_points(o3dpp_ctx *c, const double *pts, int ransac_n, int num_iterations, double *planes)
+{
+    CTX_CHECK(c);
+    if (!pts || !planes) return set_err(O3DPP_E_ARG, "null argument");
+    return planes_from_points_impl(c, pts, ransac_n, num_iterations, planes);
+}
+O3DPP_API int o3dpp_score_planes(o3dpp_ctx *c, const double *planes, int num_planes, double distance_threshold, int64_t n_use,
+                                 int64_t *counts, double *errs)
+{
+    CTX_CHECK(c);
+    if (!planes || !counts || !errs) return set_err(O3DPP_E_ARG, "null argument");
+    return score_planes_impl(c, planes, num_planes, distance_threshold, n_use, counts, errs);
+}
+O3DPP_API int o3dpp_plane_inliers(o3dpp_ctx *c, const double *plane4, double distance_threshold, int64_t n_use, int64_t *n_inliers,
+                                  double *sum3)
+{
+    CTX_CHECK(c);
+    if (!plane4) return set_err(O3DPP_E_ARG, "null argument");
+    return plane_inliers_impl(c, plane4, distance_threshold, n_use, n_inliers, sum3);
+}
+O3DPP_API int o3dpp_inlier_moments(o3dpp_ctx *c, const double *centroid3, double *mom6)
+{
+    CTX_CHECK(c);
+    if (!centroid3 || !mom6) return set_err(O3DPP_E_ARG, "null argument");
+    return inlier_moments_impl(c, centroid3, mom6);
+}
+O3DPP_API int o3dpp_fetch_kth_bound(o3dpp_ctx *c, float *out)
+{
+    CTX_CHECK(c);
+    if (!out) return set_err(O3DPP_E_ARG, "null argument");
+    return fetch_kth_impl(c, out);
+}

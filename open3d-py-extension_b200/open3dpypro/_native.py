@@ -28,7 +28,8 @@ SYMBOLS = [
     "o3dpp_size", "o3dpp_has", "o3dpp_drop", "o3dpp_bounds", "o3dpp_transform", "o3dpp_voxel",
     "o3dpp_voxel_fetch", "o3dpp_voxel_select", "o3dpp_estimate_normals", "o3dpp_knn",
     "o3dpp_segment_plane", "o3dpp_fetch_inliers", "o3dpp_fetch_samples", "o3dpp_select",
-    "o3dpp_select_inliers",
+    "o3dpp_select_inliers", "o3dpp_sample_philox", "o3dpp_planes_from_points", "o3dpp_score_planes",
+    "o3dpp_plane_inliers", "o3dpp_inlier_moments", "o3dpp_fetch_kth_bound",
 ]
 
 _lib = None
@@ -271,6 +272,57 @@ class Context:
 
     def select_inliers(self, invert=False):
         _check(lib().o3dpp_select_inliers(self._h, C.c_int(int(invert))))
+
+    # ---- the steps of segment_plane for slab-sharded scans (sharding.py)
+    def sample_philox(self, seed, n, ransac_n, num_iterations):
+        out = np.empty((int(num_iterations), int(ransac_n)), np.int64)
+        if out.size:
+            _check(lib().o3dpp_sample_philox(self._h, C.c_uint64(seed), C.c_int64(n), C.c_int(ransac_n),
+                                             C.c_int(num_iterations), _ptr(out)))
+        return out
+
+    def planes_from_points(self, pts, ransac_n):
+        pts = np.ascontiguousarray(np.asarray(pts, dtype=np.float64).reshape(-1, int(ransac_n), 3))
+        planes = np.zeros((len(pts), 4))
+        if len(pts):
+            _check(lib().o3dpp_planes_from_points(self._h, _ptr(pts), C.c_int(ransac_n), C.c_int(len(pts)), _ptr(planes)))
+        return planes
+
+    def score_planes(self, planes, distance_threshold, n_use=0):
+        planes = np.ascontiguousarray(np.asarray(planes, dtype=np.float64).reshape(-1, 4))
+        counts = np.zeros(len(planes), np.int64)
+        errs = np.zeros(len(planes), np.float64)
+        if len(planes) and self.size():
+            _check(lib().o3dpp_score_planes(self._h, _ptr(planes), C.c_int(len(planes)), C.c_double(distance_threshold),
+                                            C.c_int64(n_use), _ptr(counts), _ptr(errs)))
+        return counts, errs
+
+    def plane_inliers(self, plane, distance_threshold, n_use=0):
+        """inlier list of `plane` (kept on the device: fetch_inlier_list / select_inliers); returns (count, coordinate sums)"""
+        plane = np.ascontiguousarray(np.asarray(plane, dtype=np.float64).reshape(4))
+        m = C.c_int64(0)
+        s3 = np.zeros(3)
+        _check(lib().o3dpp_plane_inliers(self._h, _ptr(plane), C.c_double(distance_threshold), C.c_int64(n_use), C.byref(m), _ptr(s3)))
+        return m.value, s3
+
+    def fetch_inlier_list(self, m):
+        inl = np.empty(int(m), np.int32)
+        if m:
+            _check(lib().o3dpp_fetch_inliers(self._h, _ptr(inl)))
+        return inl
+
+    def inlier_moments(self, centroid):
+        cen = np.ascontiguousarray(np.asarray(centroid, dtype=np.float64).reshape(3))
+        mom = np.zeros(6)
+        _check(lib().o3dpp_inlier_moments(self._h, _ptr(cen), _ptr(mom)))
+        return mom
+
+    def kth_bound(self):
+        """per point: upper bound of the squared distance to its k-th neighbour (last estimate_normals)"""
+        out = np.empty(self.size(), np.float32)
+        if out.size:
+            _check(lib().o3dpp_fetch_kth_bound(self._h, _ptr(out)))
+        return out
 
 
 _contexts = {}

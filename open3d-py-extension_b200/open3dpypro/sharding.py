@@ -113,19 +113,28 @@ def exchange_halo(owned: np.ndarray, axis: int, cuts: Sequence[float], rank: int
     the halo points received.  One all-to-all of (n,3) float64 blocks."""
     if world == 1:
         return np.empty((0, 3))
+    send = [owned[halo_mask(owned, axis, cuts, r, halo)] if r != rank else np.empty((0, 3)) for r in range(world)]
+    got = all_to_all_rows(send, rank, world, group)
+    got = [g for r, g in enumerate(got) if r != rank and len(g)]
+    return np.concatenate(got, 0) if got else np.empty((0, 3))
+
+
+def all_to_all_rows(send: Sequence[np.ndarray], rank: int, world: int, group=None) -> List[np.ndarray]:
+    """uneven all-to-all of (n_r, 3) float64 blocks: send[r] goes to rank r; returns the block received from
+    every rank (its own block is passed through).  NCCL: one all_to_all over NVLink; gloo: pairwise isend/irecv."""
     import torch
     import torch.distributed as dist
-    send = [owned[halo_mask(owned, axis, cuts, r, halo)] if r != rank else np.empty((0, 3)) for r in range(world)]
-    counts = torch.tensor([len(s) for s in send], dtype=torch.int64, device=_dev(group))
+    counts = torch.tensor([len(x) for x in send], dtype=torch.int64, device=_dev(group))
     allc = [torch.empty_like(counts) for _ in range(world)]
     dist.all_gather(allc, counts, group=group)
     recv_counts = [int(allc[r][rank]) for r in range(world)]
-    dev = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
-    outs = [torch.from_numpy(np.ascontiguousarray(s, dtype=np.float64)).reshape(-1, 3).to(dev) for s in send]
+    dev = _dev(group)
+    outs = [torch.from_numpy(np.ascontiguousarray(x, dtype=np.float64)).reshape(-1, 3).to(dev) for x in send]
     ins = [torch.empty((c, 3), dtype=torch.float64, device=dev) for c in recv_counts]
     if dist.get_backend(group) == "nccl":
         dist.all_to_all(ins, outs, group=group)
-    else:   # gloo has no all_to_all for uneven lists: pairwise isend/irecv
+    else:   # gloo has no all_to_all for uneven lists
+        ins[rank].copy_(outs[rank])
         reqs = []
         for r in range(world):
             if r == rank:
@@ -136,8 +145,18 @@ def exchange_halo(owned: np.ndarray, axis: int, cuts: Sequence[float], rank: int
                 reqs.append(dist.irecv(ins[r], r, group=group))
         for q in reqs:
             q.wait()
-    got = [t.cpu().numpy() for r, t in enumerate(ins) if r != rank and recv_counts[r]]
-    return np.concatenate(got, 0) if got else np.empty((0, 3))
+    return [t.cpu().numpy() for t in ins]
+
+
+def redistribute(part: np.ndarray, axis: int, cuts: Sequence[float], rank: int, world: int, group=None) -> np.ndarray:
+    """every rank holds an arbitrary part of the scan; afterwards it holds the points of its own slab
+    (rank-major, original order inside every source block).  One all-to-all."""
+    part = np.asarray(part, dtype=np.float64).reshape(-1, 3)
+    if world == 1:
+        return part
+    owner = slab_of(part, axis, cuts)
+    got = all_to_all_rows([part[owner == r] for r in range(world)], rank, world, group)
+    return np.concatenate(got, 0)
 
 
 def allreduce_scores(counts: np.ndarray, errs: np.ndarray, group=None):
@@ -149,3 +168,161 @@ def allreduce_scores(counts: np.ndarray, errs: np.ndarray, group=None):
     dist.all_reduce(c, op=dist.ReduceOp.SUM, group=group)
     dist.all_reduce(e, op=dist.ReduceOp.SUM, group=group)
     return c.cpu().numpy(), e.cpu().numpy()
+
+
+# ---------------------------------------------------------------------------------- slab-sharded operators
+def _allreduce(arr: np.ndarray, op: str, group=None) -> np.ndarray:
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return np.array(arr, copy=True)
+    t = torch.from_numpy(np.ascontiguousarray(arr)).to(_dev(group))
+    dist.all_reduce(t, op={"sum": dist.ReduceOp.SUM, "max": dist.ReduceOp.MAX, "min": dist.ReduceOp.MIN}[op], group=group)
+    return t.cpu().numpy()
+
+
+def slab_estimate_normals(ctx, owned: np.ndarray, axis: int, cuts: Sequence[float], rank: int, world: int,
+                          mode: int, knn: int, radius: float = 0.0, group=None):
+    """estimate_normals of the points this rank owns, equal to the single-GPU result on the whole scan.
+
+    hybrid / radius search: one halo exchange of width `radius` (exact).  Pure KNN: a first pass over the
+    owned points alone bounds every query's k-th distance (o3dpp_fetch_kth_bound); the halo width is the
+    largest bound among the queries that could reach across a cut (all-reduce MAX), then one exchange and
+    the final pass.  Returns (normals of the owned points, info dict).  The context is left holding
+    owned + halo points (owned first)."""
+    from . import _native as nat
+    owned = np.ascontiguousarray(owned, dtype=np.float64).reshape(-1, 3)
+    n_own = len(owned)
+    info = {"halo_width": 0.0, "halo_points": 0, "passes": 1}
+    if world == 1:
+        ctx.upload(nat.ATTR_POINTS, owned)
+        ctx.drop(nat.ATTR_NORMALS)
+        ctx.estimate_normals(mode, knn, radius)
+        return _download_normals(ctx, n_own), info
+    if mode == nat.SEARCH_KNN:
+        ctx.upload(nat.ATTR_POINTS, owned)
+        ctx.drop(nat.ATTR_NORMALS)
+        h_need = 0.0
+        if n_own:
+            ctx.estimate_normals(mode, knn, radius)
+            r = np.sqrt(ctx.kth_bound().astype(np.float64)) * (1.0 + 1e-6)
+            x = owned[:, axis]
+            to_cut = np.minimum(x - cuts[rank], cuts[rank + 1] - x)        # +-inf at the outer faces
+            unsafe = r > to_cut
+            if unsafe.any():
+                h_need = float(r[unsafe].max())
+            info["passes"] = 2
+        halo_w = float(_allreduce(np.array([h_need]), "max", group)[0])
+        if not np.isfinite(halo_w):                                          # a slab with fewer than k points
+            halo_w = float(_allreduce(np.array([np.ptp(owned[:, axis]) if n_own else 0.0]), "sum", group)[0]) + 1.0
+    else:
+        halo_w = float(radius)
+    halo = exchange_halo(owned, axis, cuts, rank, world, halo_w, group)
+    info.update(halo_width=halo_w, halo_points=int(len(halo)))
+    loc = np.concatenate([owned, halo], 0) if len(halo) else owned
+    ctx.upload(nat.ATTR_POINTS, loc)
+    ctx.drop(nat.ATTR_NORMALS)
+    if len(loc):
+        ctx.estimate_normals(mode, knn, radius)
+    return _download_normals(ctx, n_own), info
+
+
+def _download_normals(ctx, n_own):
+    from . import _native as nat
+    n = ctx.size()
+    if n == 0:
+        return np.empty((0, 3))
+    out = np.empty((n, 3), np.float64)
+    ctx.download(nat.ATTR_NORMALS, out)
+    return out[:n_own]
+
+
+def ransac_select(planes: np.ndarray, counts: np.ndarray, errs: np.ndarray, n_total: int, ransac_n: int,
+                  num_iterations: int, probability: float):
+    """Open3D's serial best-so-far rule with the early-exit bound, replayed over hypotheses scored in full
+    (the same loop as csrc/ransac.cuh segment_plane_impl).  Returns (best index, best plane)."""
+    import math
+    DBL_MAX = 1.7976931348623157e308
+    best_fit, best_rmse, best, best_pl = 0.0, 0.0, -1, np.zeros(4)
+    break_iteration, it = DBL_MAX, 0
+    for h in range(int(num_iterations)):
+        if it > break_iteration:
+            break
+        pl = planes[h]
+        if not pl.any():
+            continue
+        c = int(counts[h])
+        fit = c / float(n_total) if c else 0.0
+        rmse = float(errs[h]) / math.sqrt(c) if c else 0.0
+        if fit > best_fit or (fit == best_fit and rmse < best_rmse):
+            best_fit, best_rmse, best, best_pl = fit, rmse, h, pl.copy()
+            if fit < 1.0:
+                den = math.log(1.0 - fit ** ransac_n) if fit > 0.0 else 0.0
+                num = math.log(1.0 - probability) if probability < 1.0 else -math.inf
+                bi = num / den if den != 0.0 else (-math.inf if num < 0 else math.nan)   # C: negative / +0.0
+                break_iteration = DBL_MAX if not (bi >= 0.0) else math.floor(min(bi, float(num_iterations)))
+            else:
+                break_iteration = 0.0
+        it += 1
+    return best, best_pl
+
+
+def refit_plane(centroid: np.ndarray, mom: np.ndarray) -> np.ndarray:
+    """plane through `centroid` from the six centred moments (xx, xy, xz, yy, yz, zz): Open3D GetPlaneFromPoints"""
+    import math
+    xx, xy, xz, yy, yz, zz = [float(v) for v in mom]
+    det_x, det_y, det_z = yy * zz - yz * yz, xx * zz - xz * xz, xx * yy - xy * xy
+    if det_x > det_y and det_x > det_z:
+        abc = [det_x, xz * yz - xy * zz, xy * yz - xz * yy]
+    elif det_y > det_z:
+        abc = [xz * yz - xy * zz, det_y, xy * xz - yz * xx]
+    else:
+        abc = [xy * yz - xz * yy, xy * xz - yz * xx, det_z]
+    nn = math.sqrt((abc[0] * abc[0] + abc[1] * abc[1]) + abc[2] * abc[2])
+    if nn == 0.0:
+        return np.zeros(4)
+    a, b, c = abc[0] / nn, abc[1] / nn, abc[2] / nn
+    return np.array([a, b, c, -((a * centroid[0] + b * centroid[1]) + c * centroid[2])])
+
+
+def slab_segment_plane(ctx, owned: np.ndarray, rank: int, world: int, distance_threshold: float, ransac_n: int,
+                       num_iterations: int, probability: float = 0.99999999, seed: int = 0, group=None,
+                       n_use: Optional[int] = None):
+    """segment_plane of a scan whose points are spread over the ranks.  The context must hold this rank's
+    owned points FIRST (e.g. as slab_estimate_normals left it; n_use = number of owned points).  Global point
+    index = position in the rank-major concatenation of the owned arrays; the hypothesis sequence is the
+    Philox sequence of the single-GPU call on that concatenation, so counts, winner and inlier sets are
+    identical to it (error sums differ in summation order: they only break exact count ties).
+    Returns (plane [a,b,c,d], local inlier indices into `owned` ascending, global offset of this rank, info)."""
+    owned = np.asarray(owned, dtype=np.float64).reshape(-1, 3)
+    n_own = len(owned) if n_use is None else int(n_use)
+    H, rn = int(num_iterations), int(ransac_n)
+    counts_all = _allreduce(np.eye(world, dtype=np.int64)[rank] * n_own, "sum", group) if world > 1 else np.array([n_own])
+    offset, n_total = int(counts_all[:rank].sum()), int(counts_all.sum())
+    if rn < 3:
+        raise RuntimeError("ransac_n should be set to higher than or equal to 3.")
+    if n_total < rn:
+        raise RuntimeError("There must be at least 'ransac_n' points.")
+    samples = ctx.sample_philox(seed, n_total, rn, H)                       # identical on every rank
+    pts = np.zeros((H * rn, 3))
+    flat = samples.reshape(-1)
+    mine = (flat >= offset) & (flat < offset + n_own)
+    pts[mine] = owned[flat[mine] - offset]
+    pts = _allreduce(pts, "sum", group)                                       # owners publish the sampled points
+    planes = ctx.planes_from_points(pts, rn)
+    counts, errs = ctx.score_planes(planes, distance_threshold, n_own) if n_own else (np.zeros(H, np.int64), np.zeros(H))
+    counts = _allreduce(counts, "sum", group)
+    errs = _allreduce(errs, "sum", group)
+    best, best_pl = ransac_select(planes, counts, errs, n_total, rn, H, probability)
+    m, s3 = ctx.plane_inliers(best_pl, distance_threshold, n_own) if n_own else (0, np.zeros(3))
+    tot = _allreduce(np.concatenate([[float(m)], s3]), "sum", group)
+    m_total = int(round(tot[0]))
+    plane = np.zeros(4)
+    if m_total > 0:
+        cen = tot[1:] / float(m_total)
+        mom = ctx.inlier_moments(cen) if n_own else np.zeros(6)
+        mom = _allreduce(mom, "sum", group)
+        plane = refit_plane(cen, mom)
+    inl = ctx.fetch_inlier_list(m) if n_own else np.empty(0, np.int32)
+    return plane, inl, offset, {"best_iter": best, "best_plane": best_pl, "n_inliers": m_total, "n_total": n_total,
+                                "counts": counts, "samples": samples}
