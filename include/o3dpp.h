@@ -173,6 +173,16 @@ O3DPP_API int o3dpp_inlier_moments(o3dpp_ctx *ctx, const double *centroid3, doub
  * o3dpp_estimate_normals (knn <= 32, KNN or hybrid): tells which queries near a slab cut need a wider halo */
 O3DPP_API int o3dpp_fetch_kth_bound(o3dpp_ctx *ctx, float *out);
 
+/* ---- callers either side of the path */
+/* remove_statistical_outlier (PointCloud.py:370-372 -> Open3D RemoveStatisticalOutliers): out[i] = mean distance of
+ * point i to its `knn` nearest points (itself included; summed in (d2, index) order), -1 if none */
+O3DPP_API int o3dpp_knn_mean_distance(o3dpp_ctx *ctx, int knn, double *out);
+/* ZDepthViewer splat (processors.py:859-915): z_grid[yi*grid+xi] = z of the LAST point (largest index) falling into the
+ * cell, NaN where empty; xi = clip(int32((x - x_min) / (x_max - x_min) * (grid - 1))) in float32 as numpy computes it.
+ * last_index (nullable): that point's index per cell, -1 where empty. */
+O3DPP_API int o3dpp_zsplat(o3dpp_ctx *ctx, int grid_size, double x_min, double x_max, double y_min, double y_max,
+                           float *z_grid, int32_t *last_index);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,104 @@
+// extras.cuh — the callers either side of the hot path:
+//   f2  remove_statistical_outlier (reference PointCloud.py:370-372 -> Open3D RemoveStatisticalOutliers):
+//       per point, the mean of the distances to its nb_neighbors nearest points (itself included), summed
+//       in (d2, index) order starting from 0.0 as std::accumulate does; the global mean / deviation /
+//       threshold are three scalars computed by the host side over the n means.
+//   f3  z-depth splat (reference processors.py:859-915 ZDepthViewer, test_pipeline.py:90-167): every point
+//       is dropped into a grid x grid cell from its normalised (x, y); numpy's `z_grid[yi, xi] = z` keeps the
+//       LAST point of a cell, so the kernel resolves collisions by the largest point index (atomicMax),
+//       then gathers z.  The result is a headless float32 device buffer copied to the host; no window.
+#pragma once
+#include "ransac_parts.cuh"
+
+__global__ void __launch_bounds__(256)
+mean_dist_kernel(const double *__restrict__ d2, const int32_t *__restrict__ cnt, int K, int64_t n, double *__restrict__ out)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        int c = cnt[i];
+        double s = 0.0;
+        for (int j = 0; j < c; ++j) s = __dadd_rn(s, sqrt(d2[i * K + j]));
+        out[i] = c > 0 ? s / (double)c : -1.0;
+    }
+}
+
+static int knn_mean_distance_impl(o3dpp_ctx *c, int K, double *host)
+{
+    int64_t n = c->n;
+    if (K <= 0) return set_err(O3DPP_E_ARG, "knn must be positive");
+    if (K > O3DPP_MAX_KNN) return set_err(O3DPP_E_UNSUPPORTED, "knn larger than O3DPP_MAX_KNN");
+    if (n == 0) return 0;
+    KnnOut out;
+    memset(&out, 0, sizeof out);
+    O3_TRY(c->g_nbr.ensure((size_t)n * K * 4 + 64));
+    O3_TRY(c->g_nd2.ensure((size_t)n * K * 8 + 64));
+    O3_TRY(c->g_ncnt.ensure((size_t)n * 4 + 64));
+    out.idx = c->g_nbr.as<int32_t>(); out.d2 = c->g_nd2.as<double>(); out.cnt = c->g_ncnt.as<int32_t>();
+    c->kth_valid = false;
+    GridDesc gd;
+    cudaEventRecord(c->ev[0], c->stream);
+    O3_TRY(grid_build(c, &gd));
+    O3_TRY(launch_search_mode<0>(c, gd, K, 0.0, out));
+    O3_TRY(c->s_keys0.ensure((size_t)n * 8 + 64));
+    double *means = c->s_keys0.as<double>();
+    LAUNCH(c, mean_dist_kernel, grid_for(c, n, 256, 16), 256, 0, out.d2, out.cnt, K, n, means);
+    O3_TRY(check_launch("mean_dist"));
+    cudaEventRecord(c->ev[1], c->stream);
+    O3_TRY(d2h(c, host, means, (size_t)n * 8));
+    CU_TRY(cudaStreamSynchronize(c->stream));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]);
+    c->timings[0] = ms;
+    return 0;
+}
+
+// ---- z-depth splat ------------------------------------------------------------------------------------
+// cell of a point, float32 arithmetic in the reference's order: (v - min) / (max - min) * (grid - 1), truncated, clipped
+__device__ __forceinline__ int splat_cell(float v, float lo, float hi, int grid)
+{
+    float t = __fmul_rn(__fdiv_rn(__fsub_rn(v, lo), __fsub_rn(hi, lo)), (float)(grid - 1));
+    int q = (int)t;                      // numpy astype(int32): truncation towards zero
+    return q < 0 ? 0 : (q > grid - 1 ? grid - 1 : q);
+}
+
+__global__ void __launch_bounds__(256)
+splat_index_kernel(const double *__restrict__ x, const double *__restrict__ y, int64_t n, float x0, float x1, float y0, float y1,
+                   int grid, int *__restrict__ last)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        int xi = splat_cell((float)x[i], x0, x1, grid), yi = splat_cell((float)y[i], y0, y1, grid);
+        atomicMax(last + yi * grid + xi, (int)i);
+    }
+}
+
+__global__ void splat_gather_kernel(const double *__restrict__ z, const int *__restrict__ last, int cells, float *__restrict__ zgrid)
+{
+    int cidx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cidx >= cells) return;
+    int i = last[cidx];
+    zgrid[cidx] = i >= 0 ? (float)z[i] : __int_as_float(0x7fc00000);
+}
+
+static int zsplat_impl(o3dpp_ctx *c, int grid, double x0, double x1, double y0, double y1, float *zgrid_host, int32_t *last_host)
+{
+    if (grid < 1 || grid > 16384) return set_err(O3DPP_E_ARG, "grid_size out of range");
+    int cells = grid * grid;
+    O3_TRY(c->s_hist.ensure((size_t)cells * 8 + 64));
+    int *last = c->s_hist.as<int>();
+    float *zg = (float *)(last + cells);
+    CU_TRY(cudaMemsetAsync(last, 0xff, (size_t)cells * 4, c->stream));
+    cudaEventRecord(c->ev[0], c->stream);
+    if (c->n > 0) {
+        LAUNCH(c, splat_index_kernel, grid_for(c, c->n, 256, 16), 256, 0, c->pts.x(), c->pts.y(), c->n, (float)x0, (float)x1, (float)y0,
+               (float)y1, grid, last);
+    }
+    LAUNCH(c, splat_gather_kernel, (cells + 255) / 256, 256, 0, c->pts.z(), last, cells, zg);
+    O3_TRY(check_launch("zsplat"));
+    cudaEventRecord(c->ev[1], c->stream);
+    O3_TRY(d2h(c, zgrid_host, zg, (size_t)cells * 4));
+    O3_TRY(d2h(c, last_host, last, (size_t)cells * 4));
+    CU_TRY(cudaStreamSynchronize(c->stream));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]);
+    c->timings[0] = ms;
+    return 0;
+}

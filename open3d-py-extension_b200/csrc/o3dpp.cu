@@ -2,7 +2,7 @@
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -fmad=false
 //        -Xcompiler -fPIC,-ffp-contract=off,-fvisibility=hidden -shared -o libo3dpp_b200.so o3dpp.cu
 // There is no CPU path in this library: every entry point needs a live CUDA context.
-#include "ransac_parts.cuh"
+#include "extras.cuh"
 #include <stdlib.h>
 
 #define CTX_CHECK(c)                                                      \
@@ -326,4 +326,19 @@ O3DPP_API int o3dpp_fetch_kth_bound(o3dpp_ctx *c, float *out)
     CTX_CHECK(c);
     if (!out) return set_err(O3DPP_E_ARG, "null argument");
     return fetch_kth_impl(c, out);
+}
+
+/* ---- callers either side of the path ------------------------------------------------ */
+O3DPP_API int o3dpp_knn_mean_distance(o3dpp_ctx *c, int knn, double *out)
+{
+    CTX_CHECK(c);
+    if (!out) return set_err(O3DPP_E_ARG, "null argument");
+    return knn_mean_distance_impl(c, knn, out);
+}
+O3DPP_API int o3dpp_zsplat(o3dpp_ctx *c, int grid_size, double x_min, double x_max, double y_min, double y_max, float *z_grid,
+                           int32_t *last_index)
+{
+    CTX_CHECK(c);
+    if (!z_grid) return set_err(O3DPP_E_ARG, "null argument");
+    return zsplat_impl(c, grid_size, x_min, x_max, y_min, y_max, z_grid, last_index);
 }

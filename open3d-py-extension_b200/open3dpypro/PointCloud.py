@@ -14,7 +14,7 @@ import uuid as _uuid
 
 import numpy as np
 
-from .geometry import (DeviceCloud, KDTreeSearchParamHybrid, KDTreeSearchParamKNN,  # noqa: F401
+from .geometry import (DeviceCloud, KDTreeFlann, KDTreeSearchParamHybrid, KDTreeSearchParamKNN,  # noqa: F401
                        KDTreeSearchParamRadius)
 
 
@@ -166,6 +166,24 @@ class PointCloudBase:
     def get_aabb(self):
         return self.pcd.get_min_bound(), self.pcd.get_max_bound()
 
+    # single-query KD-tree calls (reference :148-163)
+    def calc_KDtree(self):
+        self.pcd_tree = KDTreeFlann(self.pcd)
+        return self.pcd_tree
+
+    def get_KDtree(self):
+        if self.pcd_tree is None:
+            self.calc_KDtree()
+        return self.pcd_tree
+
+    def get_points_by_knn(self, point_idx, max_nn=1000000):
+        k, idx, d2 = self.get_KDtree().search_knn_vector_3d(self.pcd.points[point_idx], max_nn)
+        return k, idx, d2
+
+    def get_points_radius(self, point_idx, search_radius=30.0):
+        k, idx, d2 = self.get_KDtree().search_radius_vector_3d(self.pcd.points[point_idx], search_radius)
+        return k, idx, d2
+
     def read_pcd(self, filename, **_ignored):
         from .pcdio import read_pcd
         xyz, intensity = read_pcd(filename)
@@ -213,6 +231,27 @@ class PointCloudSelections(PointCloudBase):
     def select_by_plane(self, model, thickness=0.03, invert=False):
         return self._select_by_idx(self.get_index_by_plane(model, thickness), invert=invert)
 
+    def get_index_by_XYZ(self, comfunc=lambda Xs, Ys, Zs: np.ones(len(Xs), dtype=bool), invert=False):
+        p = self.get_points()
+        return self._bool2index(comfunc(p[:, 0], p[:, 1], p[:, 2]), invert=invert)
+
+    def select_by_XYZ(self, comfunc=lambda Xs, Ys, Zs: np.ones(len(Xs), dtype=bool), invert=False):
+        return self._select_by_idx(self.get_index_by_XYZ(comfunc), invert=invert)
+
+    def get_index_by_radius(self, r, invert=False):
+        return self.get_index_by_XYZ(lambda Xs, Ys, Zs: (Xs**2 + Ys**2 + Zs**2)**0.5 <= r, invert=invert)
+
+    def select_by_radius(self, r, invert=False):
+        return self._select_by_idx(self.get_index_by_radius(r), invert=invert)
+
+    def get_index_by_aabb(self, aabb_min, aabb_max, invert=False):
+        p = self.get_points()
+        inside = np.all((p >= np.asarray(aabb_min).reshape(1, 3)) & (p <= np.asarray(aabb_max).reshape(1, 3)), axis=1)
+        return self._bool2index(inside, invert=invert)
+
+    def select_by_aabb(self, aabb_min, aabb_max, invert=False):
+        return self._select_by_idx(self.get_index_by_aabb(aabb_min, aabb_max), invert=invert)
+
     def select_by_topN(self, n):
         return self._select_by_idx(np.arange(self.size())[:n])
 
@@ -246,6 +285,11 @@ class PointCloudUtility(PointCloudSelections):
         if down_sample_ratio <= 0 or down_sample_ratio > 1:
             return self.__class__()
         return self._select_by_idx(np.arange(self.size())[::int(1 / down_sample_ratio)])
+
+    def remove_statistical_outlier(self, nb_neighbors=20, std_ratio=2.0, print_progress=False):
+        """-> (PointCloud of the kept points, their indices): reference :370-372"""
+        idx = self.pcd.remove_statistical_outlier(nb_neighbors=nb_neighbors, std_ratio=std_ratio)[1]
+        return self._select_by_idx(idx), idx
 
     def distance2plane(self, plane):
         a, b, c, d = plane
@@ -281,6 +325,29 @@ class PointCloud(PointCloudAdvanceIO):
         return self, T
 
     rotate_by_normal = rotate_to_plane
+
+    def to_2D_Img(self, resolution=0.05, color=False):
+        """Top-down occupancy / colour image of the cloud (reference :785-823): pixel = round((p - min) / resolution),
+        later points overwrite earlier ones.  -> (img, minx, T, miny, invT, resolution, idx2img)"""
+        usecolor = bool(color and self.has_colors())
+        if color and not usecolor:
+            print('has no rgb data, cannot use color!')
+        p = self.get_points()
+        minx, miny = p[:, 0].min(), p[:, 1].min()
+        ir = 1 / resolution
+        T = np.diag([ir, ir, ir, 1.0]) @ np.array([[1., 0., 0., -minx], [0., 1., 0., -miny], [0., 0., 1., 0.], [0., 0., 0., 1.]])
+        px = ((T[:3, :3] @ p.T).T + T[:3, 3]).round().astype(int)
+        ix, iy = px[:, 0], px[:, 1]
+        sizex, sizey = ix.max(), iy.max()
+        ix = np.clip(ix, 0, sizex - 1)
+        iy = np.clip(iy, 0, sizey - 1)
+        if usecolor:
+            img = np.zeros((sizey, sizex, 3), np.uint8)
+            img[iy, ix] = (self.get_colors() * 255).astype(np.uint8)
+        else:
+            img = np.zeros((sizey, sizex), np.uint8)
+            img[iy, ix] = 255
+        return img, minx, T, miny, np.linalg.inv(T), resolution, list(zip(ix, iy))
 
     def seg_planes(self, thickness=0.01, ransac_n=3, num_iterations=450, top_n=10e9, minPointsRatio=0.1):
         """Peel planes until fewer than `minPointsRatio` of the points remain (reference :941-985).

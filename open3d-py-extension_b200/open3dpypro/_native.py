@@ -29,7 +29,7 @@ SYMBOLS = [
     "o3dpp_voxel_fetch", "o3dpp_voxel_select", "o3dpp_estimate_normals", "o3dpp_knn",
     "o3dpp_segment_plane", "o3dpp_fetch_inliers", "o3dpp_fetch_samples", "o3dpp_select",
     "o3dpp_select_inliers", "o3dpp_sample_philox", "o3dpp_planes_from_points", "o3dpp_score_planes",
-    "o3dpp_plane_inliers", "o3dpp_inlier_moments", "o3dpp_fetch_kth_bound",
+    "o3dpp_plane_inliers", "o3dpp_inlier_moments", "o3dpp_fetch_kth_bound", "o3dpp_knn_mean_distance", "o3dpp_zsplat",
 ]
 
 _lib = None
@@ -316,6 +316,21 @@ class Context:
         mom = np.zeros(6)
         _check(lib().o3dpp_inlier_moments(self._h, _ptr(cen), _ptr(mom)))
         return mom
+
+    def knn_mean_distance(self, knn):
+        out = np.empty(self.size(), np.float64)
+        if out.size:
+            _check(lib().o3dpp_knn_mean_distance(self._h, C.c_int(knn), _ptr(out)))
+        return out
+
+    def zsplat(self, grid_size, x_min, x_max, y_min, y_max):
+        """-> (float32 (grid, grid) z of the last point per cell, NaN where empty; int32 index of that point, -1 where empty)"""
+        g = int(grid_size)
+        z = np.empty((g, g), np.float32)
+        last = np.empty((g, g), np.int32)
+        _check(lib().o3dpp_zsplat(self._h, C.c_int(g), C.c_double(x_min), C.c_double(x_max), C.c_double(y_min), C.c_double(y_max),
+                                  _ptr(z), _ptr(last)))
+        return z, last
 
     def kth_bound(self):
         """per point: upper bound of the squared distance to its k-th neighbour (last estimate_normals)"""

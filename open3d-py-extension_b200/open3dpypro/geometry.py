@@ -306,3 +306,70 @@ class DeviceCloud:
         ctx = self._push(normals=False)
         mode = nat.SEARCH_KNN if radius is None else nat.SEARCH_HYBRID
         return ctx.knn(mode, int(knn), 0.0 if radius is None else float(radius))
+
+    # ---- the callers either side of the path
+    def remove_statistical_outlier(self, nb_neighbors, std_ratio, print_progress=False):
+        """-> (DeviceCloud of the kept points, kept indices ascending): Open3D RemoveStatisticalOutliers.
+        The per-point mean neighbour distances come from the device (o3dpp_knn_mean_distance); the cloud
+        mean, deviation and threshold are three scalars over those n numbers."""
+        if nb_neighbors < 1 or std_ratio <= 0:
+            raise RuntimeError("Illegal input parameters, the number of neighbors and standard deviation ratio must be positive.")
+        if not self.has_points():
+            return DeviceCloud(device=self._device), np.empty(0, np.int64)
+        ctx = self._push(normals=False)
+        avg = ctx.knn_mean_distance(int(nb_neighbors))
+        valid = avg > 0
+        nvalid = int((avg >= 0).sum())
+        if nvalid == 0:
+            return DeviceCloud(device=self._device), np.empty(0, np.int64)
+        cloud_mean = float(np.where(valid, avg, 0.0).sum()) / nvalid
+        sq = float(np.where(valid, (avg - cloud_mean) ** 2, 0.0).sum())
+        std = (sq / (nvalid - 1)) ** 0.5 if nvalid > 1 else 0.0
+        thr = cloud_mean + float(std_ratio) * std
+        idx = np.nonzero(valid & (avg < thr))[0]
+        out = DeviceCloud(device=self._device)
+        out._points = self._points[idx]
+        if self.has_normals():
+            out._normals = self._normals[idx]
+        if self.has_colors():
+            out._colors = self._colors[idx]
+        return out, idx
+
+    def zsplat(self, grid_size, x_min=None, x_max=None, y_min=None, y_max=None):
+        """ZDepthViewer's scatter (reference processors.py:876-894) on the device: float32 (grid, grid) z of the
+        last point per cell (NaN where empty) and that point's index.  Bounds default to the float32 min / max."""
+        p = self._points
+        f = lambda v, d: float(np.float32(d)) if v is None else float(v)
+        ctx = self._push(normals=False)
+        return ctx.zsplat(int(grid_size), f(x_min, p[:, 0].min()), f(x_max, p[:, 0].max()), f(y_min, p[:, 1].min()),
+                          f(y_max, p[:, 1].max()))
+
+
+class KDTreeFlann:
+    """o3d.geometry.KDTreeFlann over a DeviceCloud for the single-query calls of the reference
+    (PointCloud.py:148-163).  One query is a host job (an O(n) numpy pass, results ordered by (d2, index) as
+    the device searches order theirs); the batched searches are DeviceCloud.search_knn / o3dpp_knn."""
+
+    def __init__(self, cloud):
+        self._pts = np.asarray(cloud.points, dtype=np.float64)
+
+    def _d2(self, q):
+        d = self._pts - np.asarray(q, dtype=np.float64).reshape(1, 3)
+        return (d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2]
+
+    def search_knn_vector_3d(self, query, knn):
+        d2 = self._d2(query)
+        k = min(int(knn), len(d2))
+        order = np.lexsort((np.arange(len(d2)), d2))[:k]
+        return k, order.astype(np.int32), d2[order]
+
+    def search_radius_vector_3d(self, query, radius):
+        d2 = self._d2(query)
+        hit = np.nonzero(d2 < float(radius) * float(radius))[0]
+        order = hit[np.lexsort((hit, d2[hit]))]
+        return len(order), order.astype(np.int32), d2[order]
+
+    def search_hybrid_vector_3d(self, query, radius, max_nn):
+        k, idx, d2 = self.search_radius_vector_3d(query, radius)
+        k = min(k, int(max_nn))
+        return k, idx[:k], d2[:k]

@@ -184,6 +184,98 @@ class Processors:
             return res
 
 
+    class RadiusSelection(PointCloudMatProcessor):
+        """keep the points within `radius` of the sensor origin (reference :372-416, cpu model)"""
+        title: str = 'radius_selection'
+        radius: float = 5.0
+
+        def validate_pcd(self, idx, pcd: PointCloudMat):
+            pcd.require_ndarray()
+
+        def forward_raw(self, pcds_data, pcds_info=[], meta={}):
+            res = []
+            for pcd in pcds_data:
+                xyz = pcd[:, :3].astype(np.float64)
+                res.append(xyz[(xyz[:, 0]**2 + xyz[:, 1]**2 + xyz[:, 2]**2)**0.5 <= self.radius])   # the reference returns xyz only
+            return res
+
+    class RemoveStatisticalOutlier(_DeviceBlock):
+        """reference :486-500; the neighbour distances come from the device KNN"""
+        title: str = 'remove_statistical_outlier'
+        nb_neighbors: int = 20
+        std_ratio: float = 2.0
+        print_progress: bool = False
+
+        def validate_pcd(self, idx, pcd: PointCloudMat):
+            pcd.require_ndarray()
+
+        def forward_raw(self, pcds_data, pcds_info=[], meta={}):
+            from .geometry import DeviceCloud
+            res = []
+            for i, pcd in enumerate(pcds_data):
+                self._ctx(i)
+                cloud = DeviceCloud(_xyz(pcd), device=i % len(self.num_devices))
+                res.append(pcd[cloud.remove_statistical_outlier(self.nb_neighbors, self.std_ratio)[1]])
+            return res
+
+    class ZDepthViewer(_DeviceBlock):
+        """Z-depth image of every cloud (reference :838-927).  The scatter of the points into the grid runs on
+        the device (o3dpp_zsplat, last point of a cell wins as numpy's fancy assignment does); normalisation and
+        colour map act on the grid x grid image.  Headless: the images are kept in `_img_data`, no window is
+        opened (cv2.imshow in the reference: unavailable on this box)."""
+        title: str = 'z_depth_viewer'
+        bg: tuple = (0, 0, 0)
+        grid_size: int = 256
+        img_size: int = 0
+        _img_data: list = []
+        inf: float = 9999999999
+        x_min: float = inf
+        x_max: float = inf
+        y_min: float = inf
+        y_max: float = inf
+        z_min: float = inf
+        z_max: float = inf
+
+        def validate_pcd(self, idx, pcd: PointCloudMat):
+            pcd.require_ndarray()
+
+        def z_image(self, i, pcd):
+            g = self.grid_size
+            img = np.zeros((g, g, 3), dtype=np.uint8)
+            if len(pcd) == 0:
+                return img
+            xyz = _xyz(pcd)
+            x, y = xyz[:, 0], xyz[:, 1]
+            x_min = x.min() if self.x_min == self.inf else self.x_min
+            x_max = x.max() if self.x_max == self.inf else self.x_max
+            y_min = y.min() if self.y_min == self.inf else self.y_min
+            y_max = y.max() if self.y_max == self.inf else self.y_max
+            if x_max - x_min < 1e-5 or y_max - y_min < 1e-5:
+                return img
+            ctx = self._ctx(i)
+            ctx.upload(nat.ATTR_POINTS, xyz)
+            z_grid, _last = ctx.zsplat(g, x_min, x_max, y_min, y_max)
+            z_min = z_grid.min() if self.z_min == self.inf else self.z_min
+            z_max = z_grid.max() if self.z_max == self.inf else self.z_max
+            if np.isnan(z_grid).any():
+                z_grid = np.where(np.isnan(z_grid), z_min, z_grid)
+            with np.errstate(invalid='ignore'):
+                z_norm = np.zeros_like(z_grid) if z_max - z_min < 1e-5 else (z_grid - z_min) / (z_max - z_min)
+                z_img = (z_norm * 255).astype(np.uint8)
+            try:
+                import cv2
+                img = cv2.applyColorMap(z_img, cv2.COLORMAP_JET)
+            except ImportError:     # no colour map without OpenCV: grey levels in all three channels
+                img = np.repeat(z_img[:, :, None], 3, axis=2)
+            img[z_img == 0] = self.bg
+            img[:, :, 1] = z_img
+            return img
+
+        def forward_raw(self, pcds_data, pcds_info=[], meta={}):
+            self._img_data = [self.z_image(i, pcd) for i, pcd in enumerate(pcds_data)]
+            return pcds_data
+
+
 class PointCloudMatProcessors:
     @staticmethod
     def dumps(pipes: List[PointCloudMatProcessor]):
