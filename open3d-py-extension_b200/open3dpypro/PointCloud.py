@@ -351,28 +351,40 @@ class PointCloud(PointCloudAdvanceIO):
 
     def seg_planes(self, thickness=0.01, ransac_n=3, num_iterations=450, top_n=10e9, minPointsRatio=0.1):
         """Peel planes until fewer than `minPointsRatio` of the points remain (reference :941-985).
-        The reference's loop dies on its first pass (keyword mismatch swallowed by `except`);
-        this one runs as its docstring describes."""
-        rest, planes, pcds, aabbs = self, [], [], []
+        The reference's loop dies on its first pass (keyword mismatch swallowed by `except`); this one runs
+        as its docstring describes.  The cloud stays on the GPU across the peels: every pass is
+        o3dpp_segment_plane + o3dpp_select_inliers(invert) on the device copy, only the inlier indices
+        (4 B each) come back; the host keeps the list of surviving original indices to cut the attribute
+        arrays.  Pass i uses RANSAC seed `self.pcd.seed + i` (a random base seed if none is set)."""
+        from . import _native as nat
+        planes, pcds, aabbs = [], [], []
         n0 = self.size()
         if n0 < ransac_n:
             return planes, pcds, aabbs
-        while rest.size() / n0 > minPointsRatio:
+        ctx = nat.context(self.pcd._device)
+        ctx.upload(nat.ATTR_POINTS, self.get_points())
+        ctx.drop(nat.ATTR_NORMALS)
+        ctx.drop(nat.ATTR_COLORS)
+        alive = np.arange(n0)
+        base = self.pcd.seed if self.pcd.seed is not None else int(np.random.randint(0, 2**31 - 1))
+        while len(alive) / n0 > minPointsRatio:
             try:
-                plane, inl = rest.segment_plane(distance_threshold=thickness, ransac_n=ransac_n,
-                                                num_iterations=num_iterations)
+                plane, inl = ctx.segment_plane(float(thickness), int(ransac_n), int(num_iterations),
+                                               seed=int(base) + len(planes))
             except Exception as e:      # same containment as the reference
                 print(e)
                 break
             if len(inl) == 0:
                 break
             planes.append(plane)
-            part = rest._select_by_idx(inl)
+            part = self._select_by_idx(alive[inl])
             pcds.append(part)
             aabbs.append(part.get_aabb())
-            rest = rest._select_by_idx(inl, True)
+            ctx.select_inliers(invert=True)
+            alive = np.delete(alive, inl)
             if len(planes) > top_n:
                 break
+        rest = self._select_by_idx(alive) if len(alive) else self.__class__()
         pcds.append(rest)
         aabbs.append(rest.get_aabb())
         return planes, pcds, aabbs

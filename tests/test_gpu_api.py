@@ -120,6 +120,23 @@ def test_seg_planes_and_rotate_to_plane():
     assert np.abs(flat.get_points()[:, 2]).max() < 0.03
 
 
+def test_seg_planes_equals_oracle_peel(orc):
+    """device-resident peel == the oracle's segment_plane applied to the shrinking host cloud, pass by pass"""
+    pts = lidar_like(40000, 9)
+    pc = PointCloud(pts, rgb=np.random.default_rng(0).random((len(pts), 3)))
+    pc.pcd.seed = 100
+    planes, pcds, _ = pc.seg_planes(thickness=0.05, num_iterations=200, minPointsRatio=0.3)
+    cur, col = pts, pc.get_colors()
+    for i, plane in enumerate(planes):
+        eplane, einl = orc.segment_plane(cur, 0.05, 3, 200, orc.sample_philox(100 + i, len(cur), 3, 200))
+        assert np.abs(np.asarray(plane) - eplane).max() < 1e-9
+        assert np.array_equal(pcds[i].get_points(), cur[einl]) and np.array_equal(pcds[i].get_colors(), col[einl])
+        keep = np.ones(len(cur), bool)
+        keep[einl] = False
+        cur, col = cur[keep], col[keep]
+    assert len(planes) >= 1 and np.array_equal(pcds[-1].get_points(), cur)
+
+
 def test_resident_mode(orc):
     pts = lidar_like(30000, 5)
     pc = PointCloud(pts)
