@@ -130,6 +130,7 @@ def main():
     ap.add_argument("--points", type=int, default=10_000_000)
     ap.add_argument("--ref-points", type=int, default=10_000_000, help="bounded CPU sample size")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--inflight", type=int, default=3, help="scans in flight in the end-to-end measurement (1 = strictly serial)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -185,12 +186,13 @@ def main():
                        "ransac_score": ts[1], "ransac_scored": ts[7], "V": V})
         return plane
 
-    def e2e_step():
-        ctx.upload(nat.ATTR_POINTS, hin.array)          # H2D 24 B/point from page-locked memory
-        ctx.drop(nat.ATTR_NORMALS)
-        ctx.estimate_normals(nat.SEARCH_KNN, KNN, 0.0)
-        plane, inl = ctx.segment_plane(THR, RANSAC_N, ITERS, seed=1)   # D2H inliers + plane
-        ctx.download(nat.ATTR_NORMALS, hout.array)       # D2H 24 B/point
+    def e2e_step(lane=None):
+        c, hi, ho = lane or (ctx, hin, hout)
+        c.upload(nat.ATTR_POINTS, hi.array)            # H2D 24 B/point from page-locked memory
+        c.drop(nat.ATTR_NORMALS)
+        c.estimate_normals(nat.SEARCH_KNN, KNN, 0.0)
+        plane, inl = c.segment_plane(THR, RANSAC_N, ITERS, seed=1)   # D2H inliers + plane
+        c.download(nat.ATTR_NORMALS, ho.array)         # D2H 24 B/point
         return plane, inl
 
     scratch = []
@@ -217,13 +219,50 @@ def main():
     for _ in range(args.steps):
         plane, inl = e2e_step()
     barrier()
-    t_e2e = (time.perf_counter() - t0) * 1e3 / args.steps
+    t_e2e_serial = (time.perf_counter() - t0) * 1e3 / args.steps
+    # the same steps with two scans in flight: two host threads, each with its own library context (the C ABI is
+    # thread-safe per handle) and page-locked buffers, so that the PCIe copies of one scan overlap the kernels of
+    # the other.  Every step still uploads its own input and downloads its own normals, plane and inlier list.
+    t_e2e = t_e2e_serial
+    if args.inflight > 1:
+        lanes = [(ctx, hin, hout)]
+        for _ in range(args.inflight - 1):
+            c2 = nat.Context(local)
+            hi2 = nat.PinnedArray((N, 3), np.float64)
+            hi2.array[...] = pts
+            lanes.append((c2, hi2, nat.PinnedArray((N, 3), np.float64)))
+        for ln in lanes[1:]:
+            e2e_step(ln)
+        todo = list(range(args.steps))
+        lock = threading.Lock()
+        last = {}
+
+        def worker(ln):
+            while True:
+                with lock:
+                    if not todo:
+                        return
+                    todo.pop()
+                last[id(ln)] = e2e_step(ln)
+
+        barrier()
+        t0 = time.perf_counter()
+        th = [threading.Thread(target=worker, args=(ln,)) for ln in lanes]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        barrier()
+        t_e2e = (time.perf_counter() - t0) * 1e3 / args.steps
+        for c2, hi2, ho2 in lanes[1:]:
+            assert np.array_equal(ho2.array, hout.array), "pipelined normals differ from the serial result"
+            hi2.free(); ho2.free(); c2.close()
     n_inl = int(len(inl))
 
-    tm = torch.tensor([t_metric, t_step, t_e2e], dtype=torch.float64, device=f"cuda:{local}")
+    tm = torch.tensor([t_metric, t_step, t_e2e, t_e2e_serial], dtype=torch.float64, device=f"cuda:{local}")
     if dist is not None:
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
-    t_metric, t_step, t_e2e = [float(v) for v in tm.tolist()]
+    t_metric, t_step, t_e2e, t_e2e_serial = [float(v) for v in tm.tolist()]
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -241,6 +280,8 @@ def main():
                        "timing": "CUDA events on the library stream; max over ranks"},
             "stages_ms": med, "chain_ms_per_step": t_step,
             "e2e": {"value": world * N / (t_e2e * 1e-3) / 1e6, "unit": "Mpoints/s", "ms_per_step": t_e2e,
+                    "scans_in_flight": args.inflight, "serial_value": world * N / (t_e2e_serial * 1e-3) / 1e6,
+                    "serial_ms_per_step": t_e2e_serial,
                     "h2d_bytes_per_step": 24 * N, "d2h_bytes_per_step": 24 * N + 4 * n_inl + 32},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "knn_lane_kernel (tier 1) + knn_range_kernel + knn_exact_kernel: the whole neighbour search of one "
