@@ -101,7 +101,7 @@ struct o3dpp_ctx {
     DevBuf v_order, v_seg, v_oct, v_rep, v_rep_asc, v_count, v_centroid, v_normal, v_color, v_cubic;
 
     // KNN grid (Morton-sorted cells, 32-point cell groups and their box hierarchy)
-    DevBuf g_sx, g_sy, g_sz, g_sidx, g_box, g_nbr, g_nd2, g_ncnt;
+    DevBuf g_sx, g_sy, g_sz, g_sp4, g_sidx, g_box, g_boxf, g_nbr, g_nd2, g_ncnt;
 
     // RANSAC
     DevBuf r_samples, r_planes, r_cnt, r_err, r_inl, r_part;

@@ -33,8 +33,10 @@ struct GridDesc {
     int64_t off[KNN_MAX_LEVELS];      // offset (doubles) of the table's 6 box planes in `box`
     int64_t pitch[KNN_MAX_LEVELS];    // plane pitch (doubles)
     const double *sx, *sy, *sz;       // sorted points
+    const double4 *sp4;               // the same points as (x, y, z, 0) records: one 32-byte sector per gather
     const uint32_t *sidx;             // sorted position -> original index
     const double *box;
+    const float *boxf;                // the same boxes in FP32, rounded outwards (lo down, hi up): conservative culling
 };
 
 // ---- build -------------------------------------------------------------------------------
@@ -94,11 +96,13 @@ curve_key_kernel(const double *__restrict__ x, const double *__restrict__ y, con
 __global__ void __launch_bounds__(256)
 gather_sorted_kernel(const uint32_t *__restrict__ sidx, int64_t n, const double *__restrict__ x,
                      const double *__restrict__ y, const double *__restrict__ z, double *__restrict__ sx,
-                     double *__restrict__ sy, double *__restrict__ sz)
+                     double *__restrict__ sy, double *__restrict__ sz, double4 *__restrict__ sp4)
 {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         uint32_t j = sidx[i];
-        sx[i] = x[j]; sy[i] = y[j]; sz[i] = z[j];
+        double a = x[j], b = y[j], c = z[j];
+        sx[i] = a; sy[i] = b; sz[i] = c;
+        sp4[i] = make_double4(a, b, c, 0.0);
     }
 }
 
@@ -117,7 +121,7 @@ __device__ __forceinline__ double warp_max_d(double v)
 
 // one warp per entry of table `lvl`; children are points (lvl 0) or entries of table lvl-1
 __global__ void __launch_bounds__(256)
-box_level_kernel(GridDesc g, int lvl, double *__restrict__ box)
+box_level_kernel(GridDesc g, int lvl, double *__restrict__ box, float *__restrict__ boxf)
 {
     int64_t node = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (node >= g.cnt[lvl]) return;
@@ -140,6 +144,9 @@ box_level_kernel(GridDesc g, int lvl, double *__restrict__ box)
         int64_t p = g.pitch[lvl];
         b[node] = lo[0]; b[p + node] = lo[1]; b[2 * p + node] = lo[2];
         b[3 * p + node] = hi[0]; b[4 * p + node] = hi[1]; b[5 * p + node] = hi[2];
+        float *bf = boxf + g.off[lvl];
+        bf[node] = __double2float_rd(lo[0]); bf[p + node] = __double2float_rd(lo[1]); bf[2 * p + node] = __double2float_rd(lo[2]);
+        bf[3 * p + node] = __double2float_ru(hi[0]); bf[4 * p + node] = __double2float_ru(hi[1]); bf[5 * p + node] = __double2float_ru(hi[2]);
     }
 }
 
@@ -585,6 +592,7 @@ static int grid_build(o3dpp_ctx *c, GridDesc *gd)
     O3_TRY(c->s_vals0.ensure(nn * 4)); O3_TRY(c->s_vals1.ensure(nn * 4));
     O3_TRY(c->g_sx.ensure(nn * 8)); O3_TRY(c->g_sy.ensure(nn * 8)); O3_TRY(c->g_sz.ensure(nn * 8));
     O3_TRY(c->g_sidx.ensure(nn * 4));
+    O3_TRY(c->g_sp4.ensure(nn * 32));
     int grid = grid_for(c, n, 256, 16);
     LAUNCH(c, curve_key_kernel, grid, 256, 0, c->pts.x(), c->pts.y(), c->pts.z(), n, c->d_small.as<double>(), bits,
            c->s_keys0.as<uint64_t>());
@@ -593,7 +601,7 @@ static int grid_build(o3dpp_ctx *c, GridDesc *gd)
                             c->s_vals1.as<uint32_t>(), n, 3 * bits, &ks, &vs));
     CU_TRY(cudaMemcpyAsync(c->g_sidx.p, vs, (size_t)n * 4, cudaMemcpyDeviceToDevice, c->stream));
     LAUNCH(c, gather_sorted_kernel, grid, 256, 0, c->g_sidx.as<uint32_t>(), n, c->pts.x(), c->pts.y(), c->pts.z(),
-           c->g_sx.as<double>(), c->g_sy.as<double>(), c->g_sz.as<double>());
+           c->g_sx.as<double>(), c->g_sy.as<double>(), c->g_sz.as<double>(), c->g_sp4.as<double4>());
     // range tables
     int L = 0;
     int64_t cnt = (n + 31) / 32, off = 0;
@@ -609,13 +617,16 @@ static int grid_build(o3dpp_ctx *c, GridDesc *gd)
     if (gd->cnt[L - 1] > 32) return set_err(O3DPP_E_UNSUPPORTED, "cloud too large for the range-table depth");
     gd->levels = L;
     O3_TRY(c->g_box.ensure((size_t)off * 8 + 256));
+    O3_TRY(c->g_boxf.ensure((size_t)off * 4 + 256));
     gd->sx = c->g_sx.as<double>(); gd->sy = c->g_sy.as<double>(); gd->sz = c->g_sz.as<double>();
     gd->sidx = c->g_sidx.as<uint32_t>();
+    gd->sp4 = c->g_sp4.as<double4>();
     gd->box = c->g_box.as<double>();
+    gd->boxf = c->g_boxf.as<float>();
     for (int l = 0; l < L; ++l) {
         int64_t warps = gd->cnt[l];
         int blocks = (int)((warps * 32 + 255) / 256);
-        LAUNCH(c, box_level_kernel, blocks, 256, 0, *gd, l, c->g_box.as<double>());
+        LAUNCH(c, box_level_kernel, blocks, 256, 0, *gd, l, c->g_box.as<double>(), c->g_boxf.as<float>());
     }
     return check_launch("grid_build");
 }

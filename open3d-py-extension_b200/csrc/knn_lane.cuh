@@ -39,6 +39,15 @@
 #ifndef KL_UNR
 #define KL_UNR 4       // candidates per iteration of the two select passes
 #endif
+#ifndef KL_SB
+#define KL_SB 4         // cell groups loaded per staging batch (3 * KL_SB loads in flight per lane)
+#endif
+#ifndef KL_PIPE
+#define KL_PIPE 0       // select passes: load the next candidates before processing the current ones
+#endif
+#ifndef KL_FPF
+#define KL_FPF 1        // finish: neighbours whose FP64 coordinates are loaded together
+#endif
 #ifndef KL_ATOM
 #define KL_ATOM 1       // histogram update: 1 = shared atomic (fire and forget), 0 = load/add/store
 #endif
@@ -52,7 +61,7 @@
 struct KlWarpMem {
     // candidates, two to a 32-byte record {x0 x1 y0 y1 | z0 z1 p0 p1} so that the select passes run on packed
     // FP32 pairs (FFMA2); p = sorted position bits
-    float4 cand[KL_CAP + 8];
+    float4 cand[KL_CAP + 2 * KL_UNR];
     union {
         unsigned hist[(KL_NB + 1) * 32];                                        // [bin][lane]
         struct { float d[KL_BND * 32]; unsigned short s[KL_BND * 32]; } bnd; // [entry][lane]
@@ -89,18 +98,21 @@ struct KlStage {
     int64_t home;
     double blo[3], bhi[3], cc[3];
     double rho, rho2;
+    float flo[3], fhi[3], rho2f;     // the part's box and rho^2 in FP32, rounded outwards / up
     int n, ngroups;
     unsigned scanned;
     __device__ __forceinline__ KlStage(const GridDesc &g_, KlWarpMem &sm_) : g(g_), sm(sm_) {}
 
-    __device__ __forceinline__ double gap(int lvl, int64_t c) const
+    // lower bound of the squared box-to-box gap in FP32: the stored boxes are rounded outwards, the part's box
+    // (flo, fhi) too, and every operation rounds down, so a group that matters is never culled
+    __device__ __forceinline__ float gap(int lvl, int64_t c) const
     {
-        const double *b = g.box + g.off[lvl];
+        const float *b = g.boxf + g.off[lvl];
         int64_t p = g.pitch[lvl];
-        double gx = fmax(fmax(b[c] - bhi[0], blo[0] - b[3 * p + c]), 0.0);
-        double gy = fmax(fmax(b[p + c] - bhi[1], blo[1] - b[4 * p + c]), 0.0);
-        double gz = fmax(fmax(b[2 * p + c] - bhi[2], blo[2] - b[5 * p + c]), 0.0);
-        return (gx * gx + gy * gy) + gz * gz;
+        float gx = fmaxf(fmaxf(__fsub_rd(b[c], fhi[0]), __fsub_rd(flo[0], b[3 * p + c])), 0.f);
+        float gy = fmaxf(fmaxf(__fsub_rd(b[p + c], fhi[1]), __fsub_rd(flo[1], b[4 * p + c])), 0.f);
+        float gz = fmaxf(fmaxf(__fsub_rd(b[2 * p + c], fhi[2]), __fsub_rd(flo[2], b[5 * p + c])), 0.f);
+        return __fadd_rd(__fadd_rd(__fmul_rd(gx, gx), __fmul_rd(gy, gy)), __fmul_rd(gz, gz));
     }
 
     // phase 1: the cell groups whose box comes within rho of the part's box (the home group is staged already)
@@ -109,15 +121,15 @@ struct KlStage {
     {
         int64_t c = parent * 32 + lane;
         bool ex = c < g.cnt[LVL];
-        double gp = ex ? gap(LVL, c) : pos_inf();
+        float gp = ex ? gap(LVL, c) : KF_HUGE;
         if constexpr (LVL == 0) {
-            bool take = ex && gp <= rho2 && c != home;
+            bool take = ex && gp <= rho2f && c != home;
             unsigned m = __ballot_sync(FULL, take);
             int at = ngroups + __popc(m & ((1u << lane) - 1u));
             if (take && at < KL_GMAX) sm.v.gl[at] = (unsigned)c;
             ngroups += __popc(m);
         } else {
-            unsigned m = __ballot_sync(FULL, ex && gp <= rho2);
+            unsigned m = __ballot_sync(FULL, ex && gp <= rho2f);
             while (m && ngroups <= KL_GSPLIT) {
                 int b = __ffs(m) - 1;
                 m &= m - 1;
@@ -141,6 +153,9 @@ struct KlStage {
     __device__ __forceinline__ bool stage()
     {
         ngroups = 0;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { flo[a] = __double2float_rd(blo[a]); fhi[a] = __double2float_ru(bhi[a]); }
+        rho2f = __double2float_ru(rho2);
         switch (g.levels - 1) {
         case 0: collect<0>(0); break;
         case 1: collect<1>(0); break;
@@ -153,18 +168,18 @@ struct KlStage {
         __syncwarp();
         n = 32;
         const int64_t last = g.n - 1;
-        for (int i = 0; i < ngroups; i += 4) {
-            int64_t p[4];
-            double x[4], y[4], z[4];
+        for (int i = 0; i < ngroups; i += KL_SB) {
+            int64_t p[KL_SB];
+            double x[KL_SB], y[KL_SB], z[KL_SB];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
+            for (int k = 0; k < KL_SB; ++k) {
                 p[k] = i + k < ngroups ? (int64_t)sm.v.gl[i + k] * 32 + lane : g.n;
                 int64_t q = p[k] < last ? p[k] : last;
                 x[k] = g.sx[q]; y[k] = g.sy[q]; z[k] = g.sz[q];
             }
 #pragma unroll
-            for (int k = 0; k < 4; ++k) append(p[k], x[k], y[k], z[k]);
-            scanned += 4;
+            for (int k = 0; k < KL_SB; ++k) append(p[k], x[k], y[k], z[k]);
+            scanned += KL_SB;
             if (n > KL_CAP) return false;
         }
         return true;
@@ -207,11 +222,16 @@ __device__ __forceinline__ KlAnswer kl_select(KlWarpMem &sm, int lane, int np, i
     for (int b = 0; b < KL_NB; ++b) hist[b * 32] = 0u;
     // pass B: lane-private histogram of d2 (candidates are broadcast reads, loads issued ahead of the updates)
     const float2 nqx = make_float2(-qx, -qx), nqy = make_float2(-qy, -qy), nqz = make_float2(-qz, -qz);
+    // the next KL_UNR candidates are loaded before the current ones are processed: the compiler cannot hoist
+    // the loads itself (the histogram atomics may alias the candidate array as far as it knows)
+    float4 nx[KL_UNR];
+#pragma unroll
+    for (int u = 0; u < KL_UNR; ++u) nx[u] = cd[u];
     for (int s = 0; s < np; s += KL_UNR) {
         float4 cc[KL_UNR];
         int bb[KL_UNR];
 #pragma unroll
-        for (int u = 0; u < KL_UNR; ++u) cc[u] = cd[s + u];
+        for (int u = 0; u < KL_UNR; ++u) { if (KL_PIPE) { cc[u] = nx[u]; nx[u] = cd[s + KL_UNR + u]; } else cc[u] = cd[s + u]; }   // reads past np are padded
 #pragma unroll
         for (int u = 0; u < KL_UNR; u += 2) {
             float2 d = kl_d2pair(cc[u], cc[u + 1], nqx, nqy, nqz);
@@ -240,12 +260,14 @@ __device__ __forceinline__ KlAnswer kl_select(KlWarpMem &sm, int lane, int np, i
     float bmin = KF_HUGE;
     float *bd = sm.u.bnd.d + lane, *bdp = bd;
     unsigned short *bs = sm.u.bnd.s + lane, *bsp = bs, *nbp = sm.v.nb + lane;
+#pragma unroll
+    for (int u = 0; u < KL_UNR; ++u) nx[u] = cd[u];
     for (int s = 0; s < np; s += KL_UNR) {
         float4 cc[KL_UNR];
         float dd[KL_UNR];
         int bb[KL_UNR];
 #pragma unroll
-        for (int u = 0; u < KL_UNR; ++u) cc[u] = cd[s + u];
+        for (int u = 0; u < KL_UNR; ++u) { if (KL_PIPE) { cc[u] = nx[u]; nx[u] = cd[s + KL_UNR + u]; } else cc[u] = cd[s + u]; }
 #pragma unroll
         for (int u = 0; u < KL_UNR; u += 2) {
             float2 d = kl_d2pair(cc[u], cc[u + 1], nqx, nqy, nqz);
@@ -399,11 +421,21 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, KnnOut 
             if (A.ok && out.nx) {
                 Cumul cu;
                 cu.clear();
-                for (int j = 0; j < A.cn; ++j) {
-                    int p = kl_pos(sm.cand, sm.v.nb[j * 32 + lane]);
-                    double x = g.sx[p], y = g.sy[p], z = g.sz[p];
-                    if (MODE == 2 && !(dist2_rn(px, py, pz, x, y, z) < r2d)) continue;
-                    cu.add(x, y, z);
+                for (int j0 = 0; j0 < A.cn; j0 += KL_FPF) {        // KL_FPF neighbours' coordinates in flight
+                    double x[KL_FPF], y[KL_FPF], z[KL_FPF];
+#pragma unroll
+                    for (int u = 0; u < KL_FPF; ++u) {
+                        int j = j0 + u < A.cn ? j0 + u : A.cn - 1;
+                        int p = kl_pos(sm.cand, sm.v.nb[j * 32 + lane]);
+                        const double4 q4 = g.sp4[p];
+                        x[u] = q4.x; y[u] = q4.y; z[u] = q4.z;
+                    }
+#pragma unroll
+                    for (int u = 0; u < KL_FPF; ++u) {
+                        if (j0 + u >= A.cn) break;
+                        if (MODE == 2 && !(dist2_rn(px, py, pz, x[u], y[u], z[u]) < r2d)) continue;
+                        cu.add(x[u], y[u], z[u]);
+                    }
                 }
                 kf_store_normal(cu, g.sidx[mypos], out);
             }
@@ -453,14 +485,15 @@ struct K2WarpMem {
     unsigned oidx[K2_LIST];
 };
 
-__device__ __forceinline__ double kl_box_lb(const GridDesc &g, int lvl, int64_t c, double qx, double qy, double qz)
+// lower bound (FP32, every step rounded down, boxes stored rounded outwards) of the squared distance from q to box c
+__device__ __forceinline__ float kl_box_lb(const GridDesc &g, int lvl, int64_t c, float qxl, float qxh, float qyl, float qyh, float qzl, float qzh)
 {
-    const double *b = g.box + g.off[lvl];
+    const float *b = g.boxf + g.off[lvl];
     int64_t p = g.pitch[lvl];
-    double gx = fmax(fmax(__dsub_rn(b[c], qx), __dsub_rn(qx, b[3 * p + c])), 0.0);
-    double gy = fmax(fmax(__dsub_rn(b[p + c], qy), __dsub_rn(qy, b[4 * p + c])), 0.0);
-    double gz = fmax(fmax(__dsub_rn(b[2 * p + c], qz), __dsub_rn(qz, b[5 * p + c])), 0.0);
-    return __dadd_rn(__dadd_rn(__dmul_rn(gx, gx), __dmul_rn(gy, gy)), __dmul_rn(gz, gz));
+    float gx = fmaxf(fmaxf(__fsub_rd(b[c], qxh), __fsub_rd(qxl, b[3 * p + c])), 0.f);
+    float gy = fmaxf(fmaxf(__fsub_rd(b[p + c], qyh), __fsub_rd(qyl, b[4 * p + c])), 0.f);
+    float gz = fmaxf(fmaxf(__fsub_rd(b[2 * p + c], qzh), __fsub_rd(qzl, b[5 * p + c])), 0.f);
+    return __fadd_rd(__fadd_rd(__fmul_rd(gx, gx), __fmul_rd(gy, gy)), __fmul_rd(gz, gz));
 }
 
 template <int MODE>
@@ -469,6 +502,7 @@ struct K2Range {
     K2WarpMem &sm;
     int lane;
     double qx, qy, qz, cap, r2;
+    float fql[3], fqh[3], capf;     // the query rounded down / up and the bound rounded up, for the FP32 box test
     int cnt, K;
     __device__ __forceinline__ K2Range(const GridDesc &g_, K2WarpMem &sm_) : g(g_), sm(sm_) {}
 
@@ -522,6 +556,7 @@ struct K2Range {
 #pragma unroll
         for (int dlt = 16; dlt > 0; dlt >>= 1) kth = fmax(kth, shfl_xor_d(kth, dlt));
         cap = kth;
+        capf = __double2float_ru(kth);
         cnt = K;
         __syncwarp();
     }
@@ -531,12 +566,12 @@ struct K2Range {
     {
         int64_t c = parent * 32 + lane;
         bool ex = c < g.cnt[LVL];
-        double lb = ex ? kl_box_lb(g, LVL, c, qx, qy, qz) : pos_inf();
-        unsigned m = __ballot_sync(FULL, ex && lb <= cap);
+        float lb = ex ? kl_box_lb(g, LVL, c, fql[0], fqh[0], fql[1], fqh[1], fql[2], fqh[2]) : KF_HUGE;
+        unsigned m = __ballot_sync(FULL, ex && lb <= capf);
         // nearest child first: the bound drops early (shrink) and the far children are never opened
-        const unsigned key = __float_as_uint(__double2float_rd(lb));
+        const unsigned key = __float_as_uint(lb);
         while (m && (K2_SHRINK || cnt <= K2_LIST)) {
-            m &= __ballot_sync(FULL, lb <= cap);      // the bound may have dropped
+            m &= __ballot_sync(FULL, lb <= capf);     // the bound may have dropped
             if (!m) break;
             const bool mine = (m >> lane) & 1u;
             const unsigned kmin = __reduce_min_sync(FULL, mine ? key : 0xffffffffu);
@@ -594,6 +629,10 @@ knn_range_kernel(const GridDesc g, int K, double radius, KnnOut out, const int32
         rq.cap = cap;
         rq.qx = shfl_d(mx, i); rq.qy = shfl_d(my, i); rq.qz = shfl_d(mz, i);
         rq.cnt = 0;
+        rq.fql[0] = __double2float_rd(rq.qx); rq.fqh[0] = __double2float_ru(rq.qx);
+        rq.fql[1] = __double2float_rd(rq.qy); rq.fqh[1] = __double2float_ru(rq.qy);
+        rq.fql[2] = __double2float_rd(rq.qz); rq.fqh[2] = __double2float_ru(rq.qz);
+        rq.capf = __double2float_ru(cap);
         rq.walk();
         const int cnt = rq.cnt;
         if (cnt > K2_LIST) continue;             // (K2_SHRINK == 0) too many candidates inside the bound: tier 3
