@@ -9,6 +9,7 @@ selected round-robin per input mat (`cuda:{i % num_gpus}`, reference :206).
 """
 import json
 import multiprocessing
+import os
 from typing import List, Optional
 
 import numpy as np
@@ -32,12 +33,20 @@ class _DeviceBlock(PointCloudMatProcessor):
     process that runs the block (so blocks survive `run_async`'s JSON round trip and fork)"""
     multi_gpu: int = -1
 
-    def _ctx(self, i):
+    def _device(self, i):
+        """mat i -> cuda:{i % num_gpus} inside one process (reference :206); a process pinned to one GPU
+        (one process per GPU under torchrun: O3DPP_DEVICE = LOCAL_RANK) keeps every mat on that GPU"""
         if not self.num_gpus:
             self.devices_info(gpu=True, multi_gpu=self.multi_gpu)
             if not self.num_gpus:
-                raise nat.O3dppError(nat.lib().o3dpp_device_count and -1, "no CUDA device: this block has no CPU fallback")
-        return nat.context(i % len(self.num_devices))
+                raise nat.O3dppError(-1, "no CUDA device: this block has no CPU fallback")
+        pin = os.environ.get("O3DPP_DEVICE")
+        if pin is not None and pin != "":
+            return int(pin)
+        return i % len(self.num_devices)
+
+    def _ctx(self, i):
+        return nat.context(self._device(i))
 
 
 class Processors:
@@ -75,7 +84,10 @@ class Processors:
                 ctx.drop(nat.ATTR_NORMALS)
                 mode = nat.SEARCH_HYBRID if self.radius > 0 else nat.SEARCH_KNN
                 ctx.estimate_normals(mode, self.knn, self.radius)
-                res.append(np.hstack([pcd, ctx.download(nat.ATTR_NORMALS)]))
+                out = np.empty((len(pcd), pcd.shape[1] + 3), np.float64)      # = np.hstack([pcd, normals]) without the temporaries
+                out[:, :pcd.shape[1]] = pcd
+                out[:, pcd.shape[1]:] = ctx.download(nat.ATTR_NORMALS)
+                res.append(out)
             return res
 
     class VoxelDownsample(_DeviceBlock):
@@ -178,8 +190,10 @@ class Processors:
                 ctx.upload(nat.ATTR_POINTS, _xyz(pcd))
                 ctx.drop(nat.ATTR_NORMALS)
                 ctx.transform(T)
-                xyz = ctx.download(nat.ATTR_POINTS).astype(pcd.dtype, copy=False)
-                res.append(np.hstack([xyz, pcd[:, 3:]]) if pcd.shape[1] > 3 else xyz)
+                out = np.empty_like(pcd)                                      # = np.hstack([xyz.astype(dtype), pcd[:, 3:]])
+                out[:, :3] = ctx.download(nat.ATTR_POINTS)
+                out[:, 3:] = pcd[:, 3:]
+                res.append(out)
                 self.forward_T[i] = T.tolist()
             return res
 
@@ -213,8 +227,7 @@ class Processors:
             from .geometry import DeviceCloud
             res = []
             for i, pcd in enumerate(pcds_data):
-                self._ctx(i)
-                cloud = DeviceCloud(_xyz(pcd), device=i % len(self.num_devices))
+                cloud = DeviceCloud(_xyz(pcd), device=self._device(i))
                 res.append(pcd[cloud.remove_statistical_outlier(self.nb_neighbors, self.std_ratio)[1]])
             return res
 

@@ -237,34 +237,66 @@ def _download_normals(ctx, n_own):
     return out[:n_own]
 
 
+class RansacReplay:
+    """Open3D's serial best-so-far rule with the early-exit bound (the loop of csrc/ransac.cuh
+    segment_plane_impl), fed batch by batch so that scoring can stop as early as the
+    single-GPU path does.  feed() returns True once the iteration budget is exhausted."""
+
+    def __init__(self, n_total, ransac_n, num_iterations, probability):
+        self.n_total, self.rn, self.H, self.prob = float(n_total), int(ransac_n), int(num_iterations), float(probability)
+        self.best_fit, self.best_rmse, self.best, self.best_pl = 0.0, 0.0, -1, np.zeros(4)
+        self.break_iteration, self.it, self.h = 1.7976931348623157e308, 0, 0
+
+    def done(self):
+        return self.it > self.break_iteration or self.h >= self.H
+
+    def feed(self, planes, counts, errs):
+        import math
+        for pl, c, e in zip(planes, counts, errs):
+            if self.it > self.break_iteration:
+                break
+            h = self.h
+            self.h += 1
+            if not pl.any():
+                continue
+            c = int(c)
+            fit = c / self.n_total if c else 0.0
+            rmse = float(e) / math.sqrt(c) if c else 0.0
+            if fit > self.best_fit or (fit == self.best_fit and rmse < self.best_rmse):
+                self.best_fit, self.best_rmse, self.best, self.best_pl = fit, rmse, h, np.array(pl, dtype=np.float64)
+                if fit < 1.0:
+                    den = math.log(1.0 - fit ** self.rn) if fit > 0.0 else 0.0
+                    num = math.log(1.0 - self.prob) if self.prob < 1.0 else -math.inf
+                    bi = num / den if den != 0.0 else (-math.inf if num < 0 else math.nan)   # C: negative / +0.0
+                    self.break_iteration = 1.7976931348623157e308 if not (bi >= 0.0) else math.floor(min(bi, float(self.H)))
+                else:
+                    self.break_iteration = 0.0
+            self.it += 1
+        return self.done()
+
+
 def ransac_select(planes: np.ndarray, counts: np.ndarray, errs: np.ndarray, n_total: int, ransac_n: int,
                   num_iterations: int, probability: float):
-    """Open3D's serial best-so-far rule with the early-exit bound, replayed over hypotheses scored in full
-    (the same loop as csrc/ransac.cuh segment_plane_impl).  Returns (best index, best plane)."""
-    import math
-    DBL_MAX = 1.7976931348623157e308
-    best_fit, best_rmse, best, best_pl = 0.0, 0.0, -1, np.zeros(4)
-    break_iteration, it = DBL_MAX, 0
-    for h in range(int(num_iterations)):
-        if it > break_iteration:
+    """one-shot form of RansacReplay over hypotheses scored in full.  Returns (best index, best plane)."""
+    r = RansacReplay(n_total, ransac_n, num_iterations, probability)
+    r.feed(planes[:int(num_iterations)], counts, errs)
+    return r.best, r.best_pl
+
+
+def _score_and_select(ctx, planes, distance_threshold, n_own, n_total, rn, H, probability, group, batch=64):
+    """score the hypotheses in batches of `batch` on this rank's points, all-reduce every batch, replay the
+    selection, and stop as soon as the early-exit bound says so (exactly where the single-GPU path stops)"""
+    replay = RansacReplay(n_total, rn, H, probability)
+    counts_all = np.full(H, -1, np.int64)
+    for h0 in range(0, H, batch):
+        pl = planes[h0:h0 + batch]
+        c, e = ctx.score_planes(pl, distance_threshold, n_own) if n_own else (np.zeros(len(pl), np.int64), np.zeros(len(pl)))
+        c = _allreduce(c, "sum", group)
+        e = _allreduce(e, "sum", group)
+        counts_all[h0:h0 + len(pl)] = c
+        if replay.feed(pl, c, e):
             break
-        pl = planes[h]
-        if not pl.any():
-            continue
-        c = int(counts[h])
-        fit = c / float(n_total) if c else 0.0
-        rmse = float(errs[h]) / math.sqrt(c) if c else 0.0
-        if fit > best_fit or (fit == best_fit and rmse < best_rmse):
-            best_fit, best_rmse, best, best_pl = fit, rmse, h, pl.copy()
-            if fit < 1.0:
-                den = math.log(1.0 - fit ** ransac_n) if fit > 0.0 else 0.0
-                num = math.log(1.0 - probability) if probability < 1.0 else -math.inf
-                bi = num / den if den != 0.0 else (-math.inf if num < 0 else math.nan)   # C: negative / +0.0
-                break_iteration = DBL_MAX if not (bi >= 0.0) else math.floor(min(bi, float(num_iterations)))
-            else:
-                break_iteration = 0.0
-        it += 1
-    return best, best_pl
+    return replay.best, replay.best_pl, counts_all
 
 
 def refit_plane(centroid: np.ndarray, mom: np.ndarray) -> np.ndarray:
@@ -310,10 +342,7 @@ def slab_segment_plane(ctx, owned: np.ndarray, rank: int, world: int, distance_t
     pts[mine] = owned[flat[mine] - offset]
     pts = _allreduce(pts, "sum", group)                                       # owners publish the sampled points
     planes = ctx.planes_from_points(pts, rn)
-    counts, errs = ctx.score_planes(planes, distance_threshold, n_own) if n_own else (np.zeros(H, np.int64), np.zeros(H))
-    counts = _allreduce(counts, "sum", group)
-    errs = _allreduce(errs, "sum", group)
-    best, best_pl = ransac_select(planes, counts, errs, n_total, rn, H, probability)
+    best, best_pl, counts = _score_and_select(ctx, planes, distance_threshold, n_own, n_total, rn, H, probability, group)
     m, s3 = ctx.plane_inliers(best_pl, distance_threshold, n_own) if n_own else (0, np.zeros(3))
     tot = _allreduce(np.concatenate([[float(m)], s3]), "sum", group)
     m_total = int(round(tot[0]))
@@ -326,3 +355,169 @@ def slab_segment_plane(ctx, owned: np.ndarray, rank: int, world: int, distance_t
     inl = ctx.fetch_inlier_list(m) if n_own else np.empty(0, np.int32)
     return plane, inl, offset, {"best_iter": best, "best_plane": best_pl, "n_inliers": m_total, "n_total": n_total,
                                 "counts": counts, "samples": samples}
+
+
+# ---------------------------------------------------------------------------------- the same, device resident
+# torch CUDA tensors in, torch CUDA tensors out: ownership, halo selection and the exchanges run on the GPU
+# (NCCL all_to_all_single over NVLink) and the library reads / writes the tensors in place
+# (o3dpp_upload_dev / o3dpp_download_dev), so no (n,3) array crosses PCIe.  Same results as the numpy versions.
+def _sync_torch():
+    import torch
+    torch.cuda.current_stream().synchronize()
+
+
+def dev_slab_cuts(part, world: int, voxel_size: float, min_bound=None, group=None):
+    import torch
+    import torch.distributed as dist
+    distributed = world > 1 and dist.is_initialized()
+    big = torch.full((3,), float("inf"), dtype=torch.float64, device=part.device)
+    mn = part.min(0).values if len(part) else big
+    mx = part.max(0).values if len(part) else -big
+    t = torch.cat([mn, -mx])
+    if distributed:
+        dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
+    t = t.cpu().numpy()
+    mn, mx = t[:3].copy(), -t[3:]
+    if min_bound is None:
+        min_bound = mn
+    axis = int(np.argmax(mx - mn))
+    nvox = int(np.floor((mx[axis] - min_bound[axis]) / voxel_size)) + 1
+    stride = max(1, nvox // 65536)
+    nb = (nvox + stride - 1) // stride
+    idx = torch.div(torch.floor((part[:, axis] - float(min_bound[axis])) / voxel_size).long(), stride, rounding_mode="floor")
+    hist = torch.bincount(idx.clamp_(0, nb - 1), minlength=nb)
+    if distributed:
+        dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)
+    cum = np.cumsum(hist.cpu().numpy())
+    total = int(cum[-1])
+    cuts = [min_bound[axis]]
+    for r in range(1, world):
+        b = int(np.searchsorted(cum, total * r / world, side="left")) + 1
+        cuts.append(min_bound[axis] + min(b, nb) * stride * voxel_size)
+    cuts.append(np.inf)
+    cuts[0] = -np.inf
+    return axis, np.maximum.accumulate(np.asarray(cuts))
+
+
+def _dev_all_to_all_rows(send, in_splits, world: int, group=None):
+    """send: (sum(in_splits), 3) float64 rows grouped by destination rank -> rows received, grouped by source rank"""
+    import torch
+    import torch.distributed as dist
+    ins = torch.tensor(in_splits, dtype=torch.int64, device=send.device)
+    outs = torch.empty_like(ins)
+    dist.all_to_all_single(outs, ins, group=group)
+    out_splits = [int(v) for v in outs.tolist()]
+    recv = torch.empty((sum(out_splits), 3), dtype=send.dtype, device=send.device)
+    dist.all_to_all_single(recv, send.contiguous(), out_splits, [int(v) for v in in_splits], group=group)
+    return recv, out_splits
+
+
+def dev_redistribute(part, axis: int, cuts, rank: int, world: int, group=None):
+    import torch
+    if world == 1:
+        return part
+    inner = torch.as_tensor(np.asarray(cuts)[1:-1], dtype=part.dtype, device=part.device)
+    owner = torch.bucketize(part[:, axis].contiguous(), inner, right=True).clamp_(0, world - 1)
+    order = torch.argsort(owner, stable=True)
+    counts = torch.bincount(owner, minlength=world).tolist()
+    recv, _ = _dev_all_to_all_rows(part[order], counts, world, group)
+    return recv
+
+
+def dev_exchange_halo(owned, axis: int, cuts, rank: int, world: int, halo: float, group=None):
+    import torch
+    if world == 1:
+        return owned[:0]
+    x = owned[:, axis]
+    parts, counts = [], []
+    for r in range(world):
+        if r == rank:
+            counts.append(0)
+            continue
+        lo, hi = float(cuts[r]), float(cuts[r + 1])
+        m = ((x >= lo - halo) & (x < lo)) | ((x >= hi) & (x < hi + halo))
+        rows = owned[m]
+        parts.append(rows)
+        counts.append(len(rows))
+    send = torch.cat(parts, 0) if parts else owned[:0]
+    recv, _ = _dev_all_to_all_rows(send, counts, world, group)
+    return recv
+
+
+def dev_slab_estimate_normals(ctx, owned, axis: int, cuts, rank: int, world: int, mode: int, knn: int, radius: float = 0.0,
+                              group=None):
+    """slab_estimate_normals on device tensors: -> (normals of the owned points as a CUDA tensor, info).
+    The context is left holding owned + halo points (owned first)."""
+    import torch
+    from . import _native as nat
+    n_own = len(owned)
+    info = {"halo_width": 0.0, "halo_points": 0, "passes": 1}
+
+    def run(loc):
+        loc = loc.contiguous()
+        _sync_torch()
+        ctx.upload_dev(nat.ATTR_POINTS, loc.data_ptr(), len(loc), nat.F64)
+        ctx.drop(nat.ATTR_NORMALS)
+        if len(loc):
+            ctx.estimate_normals(mode, knn, radius)
+        return loc
+
+    if world > 1 and mode == nat.SEARCH_KNN:
+        h_need = 0.0
+        if n_own:
+            run(owned)
+            r = torch.from_numpy(ctx.kth_bound()).to(owned.device).double().sqrt_() * (1.0 + 1e-6)
+            x = owned[:, axis]
+            to_cut = torch.minimum(x - float(cuts[rank]), float(cuts[rank + 1]) - x)
+            unsafe = r > to_cut
+            if bool(unsafe.any()):
+                h_need = float(r[unsafe].max())
+            info["passes"] = 2
+        halo_w = float(_allreduce(np.array([h_need]), "max", group)[0])
+        if not np.isfinite(halo_w):
+            span = float(owned[:, axis].max() - owned[:, axis].min()) if n_own else 0.0
+            halo_w = float(_allreduce(np.array([span]), "sum", group)[0]) + 1.0
+    else:
+        halo_w = float(radius) if world > 1 else 0.0
+    halo = dev_exchange_halo(owned, axis, cuts, rank, world, halo_w, group)
+    info.update(halo_width=halo_w, halo_points=int(len(halo)))
+    loc = run(torch.cat([owned, halo], 0) if len(halo) else owned)
+    out = torch.empty((len(loc), 3), dtype=torch.float64, device=owned.device)
+    if len(loc):
+        ctx.download_dev(nat.ATTR_NORMALS, out.data_ptr(), nat.F64)
+        ctx.synchronize()
+    return out[:n_own], info
+
+
+def dev_slab_segment_plane(ctx, owned, rank: int, world: int, distance_threshold: float, ransac_n: int,
+                           num_iterations: int, probability: float = 0.99999999, seed: int = 0, group=None):
+    """slab_segment_plane with the owned points given as a CUDA tensor (only the 3H sampled points are read back)."""
+    import torch
+    n_own = len(owned)
+    H, rn = int(num_iterations), int(ransac_n)
+    counts_all = _allreduce(np.eye(world, dtype=np.int64)[rank] * n_own, "sum", group) if world > 1 else np.array([n_own])
+    offset, n_total = int(counts_all[:rank].sum()), int(counts_all.sum())
+    if rn < 3:
+        raise RuntimeError("ransac_n should be set to higher than or equal to 3.")
+    if n_total < rn:
+        raise RuntimeError("There must be at least 'ransac_n' points.")
+    samples = ctx.sample_philox(seed, n_total, rn, H)
+    flat = samples.reshape(-1)
+    mine = (flat >= offset) & (flat < offset + n_own)
+    pts = np.zeros((H * rn, 3))
+    if mine.any():
+        sel = torch.from_numpy(flat[mine] - offset).to(owned.device)
+        pts[mine] = owned[sel].cpu().numpy()
+    pts = _allreduce(pts, "sum", group)
+    planes = ctx.planes_from_points(pts, rn)
+    best, best_pl, counts = _score_and_select(ctx, planes, distance_threshold, n_own, n_total, rn, H, probability, group)
+    m, s3 = ctx.plane_inliers(best_pl, distance_threshold, n_own) if n_own else (0, np.zeros(3))
+    tot = _allreduce(np.concatenate([[float(m)], s3]), "sum", group)
+    m_total = int(round(tot[0]))
+    plane = np.zeros(4)
+    if m_total > 0:
+        cen = tot[1:] / float(m_total)
+        mom = _allreduce(ctx.inlier_moments(cen) if n_own else np.zeros(6), "sum", group)
+        plane = refit_plane(cen, mom)
+    return plane, m, offset, {"best_iter": best, "best_plane": best_pl, "n_inliers": m_total, "n_total": n_total,
+                              "counts": counts}

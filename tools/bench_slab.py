@@ -20,6 +20,8 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--points", type=int, default=20_000_000)
 ap.add_argument("--mode", default="hybrid")
 ap.add_argument("--steps", type=int, default=2)
+ap.add_argument("--device", action="store_true", help="device-resident bookkeeping (torch tensors + NCCL all_to_all_single)")
+ap.add_argument("--check", action="store_true", help="with --device: compare against the host-array path on the same input")
 a = ap.parse_args()
 rank, local, world = int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 torch.cuda.set_device(local)
@@ -35,17 +37,40 @@ def sync():
     torch.cuda.synchronize()
 
 rows = []
+part_t = torch.from_numpy(part).cuda() if a.device else None
 for step in range(a.steps + 1):
     sync(); t0 = time.perf_counter()
-    axis, cuts = sh.slab_cuts(part, world, 0.1)
-    owned = sh.redistribute(part, axis, cuts, rank, world)
-    sync(); t1 = time.perf_counter()
-    nrm, info = sh.slab_estimate_normals(ctx, owned, axis, cuts, rank, world, mode, 30, 0.5)
-    sync(); t2 = time.perf_counter()
-    plane, inl, off, pinfo = sh.slab_segment_plane(ctx, owned, rank, world, 0.05, 3, 1000, seed=1, n_use=len(owned))
+    if a.device:
+        axis, cuts = sh.dev_slab_cuts(part_t, world, 0.1)
+        owned = sh.dev_redistribute(part_t, axis, cuts, rank, world)
+        sync(); t1 = time.perf_counter()
+        nrm, info = sh.dev_slab_estimate_normals(ctx, owned, axis, cuts, rank, world, mode, 30, 0.5)
+        sync(); t2 = time.perf_counter()
+        plane, m_loc, off, pinfo = sh.dev_slab_segment_plane(ctx, owned, rank, world, 0.05, 3, 1000, seed=1)
+    else:
+        axis, cuts = sh.slab_cuts(part, world, 0.1)
+        owned = sh.redistribute(part, axis, cuts, rank, world)
+        sync(); t1 = time.perf_counter()
+        nrm, info = sh.slab_estimate_normals(ctx, owned, axis, cuts, rank, world, mode, 30, 0.5)
+        sync(); t2 = time.perf_counter()
+        plane, inl, off, pinfo = sh.slab_segment_plane(ctx, owned, rank, world, 0.05, 3, 1000, seed=1, n_use=len(owned))
     sync(); t3 = time.perf_counter()
     if step:
         rows.append([t1 - t0, t2 - t1, t3 - t2, t3 - t0])
+checked = None
+if a.device and a.check:
+    inl_dev = ctx.fetch_inlier_list(m_loc)
+    axis2, cuts2 = sh.slab_cuts(part, world, 0.1)
+    owned2 = sh.redistribute(part, axis2, cuts2, rank, world)
+    nrm2, info2 = sh.slab_estimate_normals(ctx, owned2, axis2, cuts2, rank, world, mode, 30, 0.5)
+    plane2, inl2, off2, pinfo2 = sh.slab_segment_plane(ctx, owned2, rank, world, 0.05, 3, 1000, seed=1, n_use=len(owned2))
+    ok = (axis == axis2 and np.array_equal(cuts, cuts2) and np.array_equal(owned.cpu().numpy(), owned2)
+          and np.array_equal(nrm.cpu().numpy(), nrm2) and np.array_equal(plane, plane2) and np.array_equal(inl_dev, inl2)
+          and info["halo_points"] == info2["halo_points"])
+    okt = torch.tensor([1.0 if ok else 0.0], device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+    checked = bool(okt.item() == 1.0)
 t = torch.tensor(rows, dtype=torch.float64, device=f"cuda:{local}").mean(0)
 cnt = torch.tensor([len(owned), info["halo_points"]], dtype=torch.float64, device=f"cuda:{local}")
 if world > 1:
@@ -59,7 +84,8 @@ if rank == 0:
                       "n_gpus": world, "steps": a.steps, "cut_redistribute_s": t[0], "normals_s": t[1], "segment_s": t[2], "total_s": t[3],
                       "mpoints_per_s_normals_segment": a.points / (t[1] + t[2]) / 1e6, "max_owned_points": int(mx[0]), "max_halo_points": int(mx[1]),
                       "halo_width": info["halo_width"], "plane": [float(v) for v in plane], "n_inliers": pinfo["n_inliers"],
-                      "note": "host numpy masks/concatenates and H2D/D2H of every stage are inside these times"}))
+                      "bookkeeping": "device tensors + NCCL all_to_all_single" if a.device else "host numpy + all_to_all of host blocks",
+                      "equal_to_host_path": checked}))
 ctx.close()
 if world > 1:
     dist.destroy_process_group()
