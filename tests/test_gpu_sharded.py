@@ -62,6 +62,29 @@ def test_parts_equal_segment_plane_single_rank(ctx):
     assert np.array_equal(info["counts"][scored], dbg["counts"][scored])
 
 
+@pytest.mark.gpu
+def test_device_resident_path_equals_host_path_single_rank(ctx):
+    """dev_slab_* (torch CUDA tensors, in-place library I/O) == slab_* (host arrays) at world = 1; the world-2 NCCL
+    comparison is `tools/bench_slab.py --device --check` (profiles/r01f_slab2_dev_hybrid.json: equal_to_host_path)"""
+    import torch
+    from open3dpypro import _native as nat
+    from open3dpypro import sharding as sh
+    from open3dpypro.synthetic import lidar_like
+    pts = lidar_like(100_000, 12).astype(np.float64)
+    t = torch.from_numpy(pts).cuda()
+    axis, cuts = sh.slab_cuts(pts, 1, 0.1)
+    axis_d, cuts_d = sh.dev_slab_cuts(t, 1, 0.1)
+    assert axis == axis_d and np.array_equal(cuts, cuts_d)
+    for mode, radius in ((nat.SEARCH_KNN, 0.0), (nat.SEARCH_HYBRID, 0.5)):
+        n_h, _ = sh.slab_estimate_normals(ctx, pts, axis, cuts, 0, 1, mode, 30, radius)
+        n_d, _ = sh.dev_slab_estimate_normals(ctx, t, axis, cuts, 0, 1, mode, 30, radius)
+        assert np.array_equal(n_d.cpu().numpy(), n_h)
+    p_h, inl_h, _, info_h = sh.slab_segment_plane(ctx, pts, 0, 1, 0.05, 3, 300, seed=4)
+    p_d, m_d, _, info_d = sh.dev_slab_segment_plane(ctx, t, 0, 1, 0.05, 3, 300, seed=4)
+    assert np.array_equal(p_h, p_d) and m_d == len(inl_h) and info_h["best_iter"] == info_d["best_iter"]
+    assert np.array_equal(ctx.fetch_inlier_list(m_d), inl_h)
+
+
 def _worker(rank, world, port, q):
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "open3d-py-extension_b200"))
