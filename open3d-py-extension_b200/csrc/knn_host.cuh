@@ -39,8 +39,15 @@ static int launch_lane(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, c
     int64_t blocks = (gd.cnt[0] + KL_WARPS - 1) / KL_WARPS;
     float rho = 0.4f;          // staging radius / part-box diagonal (measured optimum on the LiDAR-like scans)
     if (const char *e = getenv("O3DPP_KNN_RHO")) { float v = (float)atof(e); if (v > 0.f) rho = v; }
+    // a part whose grown box overflows the staging area retries with the radius shrunk (x shrink, up to max_shrink
+    // times), then is halved (never, at the default 12); gsplit = cell groups to scan beyond which an attempt is abandoned before scanning
+    int max_shrink = 12, gsplit = 96;
+    float shrink = 0.7f;
+    if (const char *e = getenv("O3DPP_KNN_MAXSHRINK")) { int v = atoi(e); if (v >= 0 && v <= 12) max_shrink = v; }
+    if (const char *e = getenv("O3DPP_KNN_GSPLIT")) { int v = atoi(e); if (v >= 16 && v <= KL_GMAX - 64) gsplit = v; }
+    if (const char *e = getenv("O3DPP_KNN_SHRINK")) { float v = (float)atof(e); if (v > 0.1f && v < 0.99f) shrink = v; }
     cudaEventRecord(c->ev[3], c->stream);
-    LAUNCH(c, k1, (int)blocks, KL_WARPS * 32, smem, gd, K, radius, rho, out, capbuf);
+    LAUNCH(c, k1, (int)blocks, KL_WARPS * 32, smem, gd, K, radius, rho, max_shrink, gsplit, shrink, out, capbuf);
     O3_TRY(check_launch("knn_lane"));
     cudaEventRecord(c->ev[4], c->stream);
     int64_t m2 = 0, m3 = 0;

@@ -99,7 +99,7 @@ struct KlStage {
     double blo[3], bhi[3], cc[3];
     double rho, rho2;
     float flo[3], fhi[3], rho2f;     // the part's box and rho^2 in FP32, rounded outwards / up
-    int n, ngroups;
+    int n, ngroups, gsplit;
     unsigned scanned;
     __device__ __forceinline__ KlStage(const GridDesc &g_, KlWarpMem &sm_) : g(g_), sm(sm_) {}
 
@@ -130,7 +130,7 @@ struct KlStage {
             ngroups += __popc(m);
         } else {
             unsigned m = __ballot_sync(FULL, ex && gp <= rho2f);
-            while (m && ngroups <= KL_GSPLIT) {
+            while (m && ngroups <= gsplit) {
                 int b = __ffs(m) - 1;
                 m &= m - 1;
                 collect<LVL - 1>(parent * 32 + b);
@@ -164,7 +164,7 @@ struct KlStage {
         case 4: collect<4>(0); break;
         default: collect<5>(0); break;
         }
-        if (ngroups > KL_GSPLIT) return false;
+        if (ngroups > gsplit) return false;
         __syncwarp();
         n = 32;
         const int64_t last = g.n - 1;
@@ -321,7 +321,8 @@ __device__ __forceinline__ KlAnswer kl_select(KlWarpMem &sm, int lane, int np, i
 // 20 fail-rho, 21 fail-boundary-overflow, 22 fail-count, 23 fail-not-staged, 24 restages, 25 parts
 template <int MODE>
 __global__ void __launch_bounds__(KL_WARPS * 32, KL_MINB)
-knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, KnnOut out, float *__restrict__ capbuf)
+knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, int max_shrink, int gsplit, float shrink, KnnOut out,
+                float *__restrict__ capbuf)
 {
     extern __shared__ __align__(16) unsigned char kl_smem[];
     const int lane = lane_id(), w = threadIdx.x >> 5;
@@ -338,7 +339,7 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, KnnOut 
 
     const long long t_start = out.stats ? clock64() : 0;
     KlStage sg(g, sm);
-    sg.lane = lane; sg.scanned = 0; sg.home = leaf_id;
+    sg.lane = lane; sg.scanned = 0; sg.home = leaf_id; sg.gsplit = gsplit;
     // the home box; candidate coordinates are relative to its centre for every part of the group
     double hlo[3], hhi[3];
     {
@@ -391,10 +392,14 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, KnnOut 
             sg.rho = rho; sg.rho2 = rho * rho * (1.0 + 1e-12);
             if (sg.stage()) break;
             restage++;
-            if (len > 4 || attempt >= 6) { staged = false; break; }
-            rho *= 0.7;
+            // a smaller radius: the sparse queries of the part then go to tier 2, the dense ones stay, and the retry
+            // costs one cheap table walk.  A part that still does not fit after max_shrink retries has a box that is
+            // itself too large (sparse points spanning dense structures): it is halved if max_shrink < 12, else all
+            // its queries go on to tiers 2 / 3 (measured: cheaper than the extra staging passes of the halves)
+            if (attempt >= (len > 4 ? max_shrink : 12)) { staged = false; break; }
+            rho *= (double)shrink;
         }
-        if (!staged && len > 4) { len >>= 1; __syncwarp(); continue; }
+        if (!staged && len > 4 && max_shrink < 12) { len >>= 1; __syncwarp(); continue; }
         parts++;
         const int ncand = staged ? sg.n : 32;
         candsum += ncand;
