@@ -54,6 +54,9 @@
 #ifndef KL_MINB
 #define KL_MINB 12
 #endif
+#ifndef KL_WIN
+#define KL_WIN 2        // unstageable parts: cell groups taken before and after the home group along the curve
+#endif
 #ifndef KL_BND
 #define KL_BND 24       // boundary-bin list entries per query
 #endif
@@ -401,13 +404,37 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, int max
         }
         if (!staged && len > 4 && max_shrink < 12) { len >>= 1; __syncwarp(); continue; }
         parts++;
-        const int ncand = staged ? sg.n : 32;
+        // a part that cannot be staged (its own box spans dense structures): stage the KL_WIN cell groups before and
+        // after the home group along the curve, unfiltered.  Nothing can be certified against them, but the k-th d2
+        // among them is a tight upper bound (tools/knn_stage_study.py: 1.17x the true k-th distance in the median),
+        // which lets tier 2 answer these queries instead of the exact search of tier 3.
+        bool window = false;
+        double wmax = 0.0;
+        if (!staged && nq >= K) {
+            window = true;
+            sg.n = 32;
+#pragma unroll
+            for (int dlt = -KL_WIN; dlt <= KL_WIN; ++dlt) {
+                const int64_t leaf = leaf_id + dlt, p = leaf * 32 + lane;
+                const bool v = dlt != 0 && leaf >= 0 && p < g.n;
+                double lx = 0, ly = 0, lz = 0;
+                if (v) { lx = g.sx[p] - sg.cc[0]; ly = g.sy[p] - sg.cc[1]; lz = g.sz[p] - sg.cc[2]; }
+                const unsigned m = __ballot_sync(FULL, v);
+                if (v) {
+                    kl_put(sm.cand, sg.n + __popc(m & ((1u << lane) - 1u)), (float)lx, (float)ly, (float)lz, (int)p);
+                    wmax = fmax(wmax, fmax(fmax(fabs(lx), fabs(ly)), fabs(lz)));
+                }
+                sg.n += __popc(m);
+            }
+            wmax = warp_max_d(wmax);
+        }
+        const int ncand = (staged || window) ? sg.n : 32;
         candsum += ncand;
         const int np = (ncand + KL_UNR - 1) & ~(KL_UNR - 1);
         if (lane < np - ncand) kl_put(sm.cand, ncand + lane, KF_BIG, KF_BIG, KF_BIG, -1);
         __syncwarp();
-        // error model of the staged FP32 coordinates: |coordinate| <= half home extent + rho
-        const float Lf = (float)((0.5 * hext + rho) * 1.001);
+        // error model of the staged FP32 coordinates: |coordinate| <= half home extent + rho (window: the largest staged)
+        const float Lf = (float)((window ? fmax(0.5 * hext, wmax) : 0.5 * hext + rho) * 1.001);
         const float eA = 16.0f * KF_U * Lf, eC = 2.3e-13f * Lf * Lf;
         const float rho1f = staged ? __double2float_rd(rho * rho * (1.0 - 1e-6)) : -1.0f;
         float tcap = KF_TCAP;
@@ -418,8 +445,10 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, int max
         }
         KlAnswer A;
         A.ok = false; A.cn = 0; A.why = 5; A.capf = __int_as_float(0x7f800000);
-        if (nq >= K && staged) A = kl_select<MODE>(sm, lane, np, K, qx, qy, qz, U, tcap, rho1f, eA, eC);
-        else if (nq >= K) A.capf = U + kf_err(U, eA, eC) * 1.0001f;
+        if (nq >= K && (staged || window)) {
+            A = kl_select<MODE>(sm, lane, np, K, qx, qy, qz, U, tcap, rho1f, eA, eC);
+            if (window) { A.ok = false; A.why = 5; }      // rho1f < 0 already refuses; the bound A.capf is what counts
+        } else if (nq >= K) A.capf = U + kf_err(U, eA, eC) * 1.0001f;
         if (inpart && valid) {
             capbuf[mypos] = A.ok ? -fmaxf(A.capf, 1e-30f) : A.capf;   // negative = answered, magnitude bounds the k-th d2
             if (out.stats) { n1 += A.why == 1; n2 += A.why == 2; n3 += A.why == 3; n4 += A.why == 4; n5 += A.why == 5; }
