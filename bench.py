@@ -191,8 +191,9 @@ def main():
         c.upload(nat.ATTR_POINTS, hi.array)            # H2D 24 B/point from page-locked memory
         c.drop(nat.ATTR_NORMALS)
         c.estimate_normals(nat.SEARCH_KNN, KNN, 0.0)
+        c.download_async(nat.ATTR_NORMALS, ho.array)   # D2H 24 B/point, on the copy stream while segment_plane runs
         plane, inl = c.segment_plane(THR, RANSAC_N, ITERS, seed=1)   # D2H inliers + plane
-        c.download(nat.ATTR_NORMALS, ho.array)         # D2H 24 B/point
+        c.synchronize()                                # normals complete on the host
         return plane, inl
 
     scratch = []

@@ -86,6 +86,11 @@ O3DPP_API int o3dpp_upload_dev(o3dpp_ctx *ctx, int attr, uintptr_t dev, int64_t 
 /* replaces np.asarray(pcd.points / normals / colors) (PointCloud.py:119-126): float64 (n,3) */
 O3DPP_API int o3dpp_download(o3dpp_ctx *ctx, int attr, double *host);
 O3DPP_API int o3dpp_download_dev(o3dpp_ctx *ctx, int attr, uintptr_t dev, int dtype);
+/* as o3dpp_download, but returns at once: the copy runs on a second stream after the work already queued and overlaps
+ * the calls that follow (e.g. the normals travel to the host while o3dpp_segment_plane runs; np.asarray(pcd.normals)
+ * of PointCloud.py:125 is then free).  `host` (page-locked for a real overlap) is complete, and the attribute may be
+ * modified again, after o3dpp_synchronize(). */
+O3DPP_API int o3dpp_download_async(o3dpp_ctx *ctx, int attr, double *host);
 O3DPP_API int o3dpp_size(o3dpp_ctx *ctx, int64_t *n);
 O3DPP_API int o3dpp_has(o3dpp_ctx *ctx, int attr, int *flag);
 O3DPP_API int o3dpp_drop(o3dpp_ctx *ctx, int attr);

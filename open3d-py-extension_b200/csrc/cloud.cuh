@@ -133,6 +133,33 @@ static int download_impl(o3dpp_ctx *c, int attr, void *dst, bool dst_is_device, 
     return 0;
 }
 
+// device -> host copy of one attribute that returns at once: the rows are interleaved and copied on a second stream,
+// ordered after everything already queued on the main stream.  The host buffer (page-locked for a real overlap) is
+// complete, and the attribute may be modified again, after o3dpp_synchronize().
+static int download_async_impl(o3dpp_ctx *c, int attr, double *dst)
+{
+    Attr3 *a = attr_of(c, attr);
+    if (!a) return set_err(O3DPP_E_ARG, "unknown attribute");
+    if (!a->present) return set_err(O3DPP_E_STATE, "attribute not present");
+    int64_t n = c->n;
+    if (n == 0) return 0;
+    if (!dst) return set_err(O3DPP_E_ARG, "null destination");
+    if (!c->copy_stream) {
+        CU_TRY(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+        CU_TRY(cudaEventCreateWithFlags(&c->copy_ev, cudaEventDisableTiming));
+    }
+    CU_TRY(cudaStreamSynchronize(c->copy_stream));          // stage2 may still feed an earlier copy
+    O3_TRY(c->stage2.ensure((size_t)n * 24));
+    CU_TRY(cudaEventRecord(c->copy_ev, c->stream));
+    CU_TRY(cudaStreamWaitEvent(c->copy_stream, c->copy_ev, 0));
+    int grid = grid_for(c, (n + 255) / 256, 1, 16);
+    interleave_kernel<double><<<grid, 256, 0, c->copy_stream>>>(a->x(), a->y(), a->z(), n, c->stage2.as<double>());
+    c->launches++;
+    O3_TRY(check_launch("interleave"));
+    CU_TRY(cudaMemcpyAsync(dst, c->stage2.p, (size_t)n * 24, cudaMemcpyDeviceToHost, c->copy_stream));
+    return 0;
+}
+
 // ---- bounds ------------------------------------------------------------------------------
 // min/max are order independent, so any reduction tree equals Open3D's serial loop.
 #define BND_THREADS 256

@@ -77,6 +77,9 @@ struct o3dpp_ctx {
     int device = 0;
     int sm_count = O3_SM_COUNT_FALLBACK;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;   // o3dpp_download_async: device->host copies that overlap the next kernels
+    cudaEvent_t copy_ev = nullptr;
+    DevBuf stage2;                        // interleaved rows of an asynchronous download
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     uint64_t launches = 0;
     double timings[8] = {0, 0, 0, 0, 0, 0, 0, 0};

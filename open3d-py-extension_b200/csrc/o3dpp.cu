@@ -54,6 +54,8 @@ O3DPP_API int o3dpp_destroy(o3dpp_ctx *c)
     if (!c) return 0;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); cudaEventDestroy(c->copy_ev); }
+    c->stage2.release();
     DevBuf *bufs[] = {&c->pts.buf, &c->nrm.buf, &c->col.buf, &c->stage, &c->d_small, &c->s_keys0, &c->s_keys1,
                       &c->s_vals0, &c->s_vals1, &c->s_hist, &c->s_scan, &c->s_scan2, &c->s_flags, &c->v_order,
                       &c->v_seg, &c->v_oct, &c->v_rep, &c->v_rep_asc, &c->v_count, &c->v_centroid, &c->v_normal,
@@ -71,6 +73,7 @@ O3DPP_API int o3dpp_synchronize(o3dpp_ctx *c)
 {
     CTX_CHECK(c);
     CU_TRY(cudaStreamSynchronize(c->stream));
+    if (c->copy_stream) CU_TRY(cudaStreamSynchronize(c->copy_stream));
     return 0;
 }
 
@@ -137,6 +140,12 @@ O3DPP_API int o3dpp_download(o3dpp_ctx *c, int attr, double *host)
 {
     CTX_CHECK(c);
     return download_impl(c, attr, host, false, O3DPP_F64);
+}
+
+O3DPP_API int o3dpp_download_async(o3dpp_ctx *c, int attr, double *host)
+{
+    CTX_CHECK(c);
+    return download_async_impl(c, attr, host);
 }
 
 O3DPP_API int o3dpp_download_dev(o3dpp_ctx *c, int attr, uintptr_t dev, int dtype)

@@ -29,7 +29,7 @@ SYMBOLS = [
     "o3dpp_voxel_fetch", "o3dpp_voxel_select", "o3dpp_estimate_normals", "o3dpp_knn",
     "o3dpp_segment_plane", "o3dpp_fetch_inliers", "o3dpp_fetch_samples", "o3dpp_select",
     "o3dpp_select_inliers", "o3dpp_sample_philox", "o3dpp_planes_from_points", "o3dpp_score_planes",
-    "o3dpp_plane_inliers", "o3dpp_inlier_moments", "o3dpp_fetch_kth_bound", "o3dpp_knn_mean_distance", "o3dpp_zsplat",
+    "o3dpp_plane_inliers", "o3dpp_inlier_moments", "o3dpp_fetch_kth_bound", "o3dpp_knn_mean_distance", "o3dpp_zsplat", "o3dpp_download_async",
 ]
 
 _lib = None
@@ -150,6 +150,14 @@ class Context:
         assert out.dtype == np.float64 and out.flags.c_contiguous and out.shape == (n, 3)
         if n:
             _check(lib().o3dpp_download(self._h, C.c_int(attr), _ptr(out)))
+        return out
+
+    def download_async(self, attr, out):
+        """starts the copy and returns; `out` is complete after synchronize()"""
+        n = self.size()
+        assert out.dtype == np.float64 and out.flags.c_contiguous and out.shape == (n, 3)
+        if n:
+            _check(lib().o3dpp_download_async(self._h, C.c_int(attr), _ptr(out)))
         return out
 
     def download_dev(self, attr, dev_ptr, dtype=F64):

@@ -178,3 +178,19 @@ def test_blocks_pipeline(orc):
     down = vox.forward_raw([frames[2]])[0]
     ref = orc.voxel_trace(src, 0.2)
     assert np.array_equal(down, frames[2][ref["rep"]])
+
+
+def test_download_async_overlaps_and_matches():
+    """o3dpp_download_async: the normals travel on the copy stream while segment_plane runs; same bytes as download"""
+    from open3dpypro import _native as nat
+    pts = lidar_like(200_000, 14)
+    c = nat.Context(0)
+    c.upload(nat.ATTR_POINTS, pts)
+    c.estimate_normals(nat.SEARCH_KNN, 30, 0.0)
+    buf = nat.PinnedArray((len(pts), 3), np.float64)
+    c.download_async(nat.ATTR_NORMALS, buf.array)
+    plane, inl = c.segment_plane(0.05, 3, 100, seed=1)
+    c.synchronize()
+    assert np.array_equal(buf.array, c.download(nat.ATTR_NORMALS)) and len(inl) > 0
+    buf.free()
+    c.close()
