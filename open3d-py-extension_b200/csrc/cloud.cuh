@@ -368,7 +368,7 @@ static int apply_selection(o3dpp_ctx *c, const int32_t *d_sel, int64_t m)
 static int select_impl(o3dpp_ctx *c, const int32_t *d_idx, int64_t m, int invert)
 {
     int64_t n = c->n;
-    DevBuf flags, sel;
+    DevBuf &flags = c->sel_flags, &sel = c->sel_idx;
     O3_TRY(flags.ensure((size_t)n + 64));
     O3_TRY(sel.ensure(((size_t)n + 64) * sizeof(int32_t)));
     int rc = 0;
@@ -384,7 +384,5 @@ static int select_impl(o3dpp_ctx *c, const int32_t *d_idx, int64_t m, int invert
         rc = apply_selection(c, sel.as<int32_t>(), cnt);
     } while (0);
     cudaStreamSynchronize(c->stream);
-    flags.release();
-    sel.release();
     return rc;
 }

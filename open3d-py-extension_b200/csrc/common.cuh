@@ -101,7 +101,8 @@ struct o3dpp_ctx {
     bool vox_valid = false;
     bool kth_valid = false;               // g_ncnt holds the per-query k-th distance bounds of the last estimate_normals
     int64_t vox_V = 0, vox_n = 0;
-    DevBuf v_order, v_seg, v_oct, v_rep, v_rep_asc, v_count, v_centroid, v_normal, v_color, v_cubic;
+    DevBuf v_order, v_seg, v_oct, v_rep, v_rep_asc, v_count, v_centroid, v_normal, v_color, v_cubic, v_flags;
+    DevBuf sel_flags, sel_idx;            // select_by_index scratch (kept: cudaMalloc/cudaFree per call cost more than the kernels)
 
     // KNN grid (Morton-sorted cells, 32-point cell groups and their box hierarchy)
     DevBuf g_sx, g_sy, g_sz, g_sp4, g_sidx, g_box, g_boxf, g_nbr, g_nd2, g_ncnt;

@@ -55,7 +55,7 @@ O3DPP_API int o3dpp_destroy(o3dpp_ctx *c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); cudaEventDestroy(c->copy_ev); }
-    c->stage2.release();
+    c->stage2.release(); c->v_flags.release(); c->sel_flags.release(); c->sel_idx.release();
     DevBuf *bufs[] = {&c->pts.buf, &c->nrm.buf, &c->col.buf, &c->stage, &c->d_small, &c->s_keys0, &c->s_keys1,
                       &c->s_vals0, &c->s_vals1, &c->s_hist, &c->s_scan, &c->s_scan2, &c->s_flags, &c->v_order,
                       &c->v_seg, &c->v_oct, &c->v_rep, &c->v_rep_asc, &c->v_count, &c->v_centroid, &c->v_normal,

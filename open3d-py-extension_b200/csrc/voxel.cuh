@@ -182,7 +182,7 @@ static int voxel_impl(o3dpp_ctx *c, double voxel_size, int64_t *Vout)
     O3_TRY(c->v_rep.ensure(vv * 4)); O3_TRY(c->v_rep_asc.ensure(vv * 4)); O3_TRY(c->v_count.ensure(vv * 4));
     O3_TRY(c->v_centroid.ensure(vv * 24)); O3_TRY(c->v_normal.ensure(vv * 24)); O3_TRY(c->v_color.ensure(vv * 24));
     O3_TRY(c->v_cubic.ensure(vv * 32));
-    DevBuf flags;
+    DevBuf &flags = c->v_flags;
     O3_TRY(flags.ensure(nn));
     CU_TRY(cudaMemsetAsync(flags.p, 0, nn, c->stream));
     bool hn = c->nrm.present, hc = c->col.present;
@@ -200,7 +200,7 @@ static int voxel_impl(o3dpp_ctx *c, double voxel_size, int64_t *Vout)
     }
     cudaEventRecord(c->ev[1], c->stream);
     cudaStreamSynchronize(c->stream);
-    flags.release(); wide_lo.release(); wide_ix.release();
+    wide_lo.release(); wide_ix.release();
     if (rc) return rc;
     if (V2 != V) return set_err(O3DPP_E_CUDA, "internal: representative count differs from row count");
     c->vox_valid = true;
