@@ -15,6 +15,7 @@ At N > 1 every rank owns its own scan (frame/scan sharding, no data-path collect
 CPU path; the Open3D wheel itself is not installable here) on the host cores.
 """
 import argparse
+import contextlib
 import json
 import os
 import statistics
@@ -130,7 +131,9 @@ def main():
     ap.add_argument("--points", type=int, default=10_000_000)
     ap.add_argument("--ref-points", type=int, default=10_000_000, help="bounded CPU sample size")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--inflight", type=int, default=3, help="scans in flight in the end-to-end measurement (1 = strictly serial)")
+    ap.add_argument("--no-token", dest="token", action="store_false",
+                    help="end-to-end lanes: let the kernels of several scans share the GPU instead of taking turns")
+    ap.add_argument("--inflight", type=int, default=2, help="scans in flight in the end-to-end measurement (1 = strictly serial)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -165,6 +168,7 @@ def main():
     hin = nat.PinnedArray((N, 3), np.float64)
     hin.array[...] = pts
     hout = nat.PinnedArray((N, 3), np.float64)
+    hinl = nat.PinnedArray((N,), np.int32)       # page-locked home of the inlier list
     ctx.upload(nat.ATTR_POINTS, hin.array)
 
     def device_step(stages):
@@ -186,13 +190,26 @@ def main():
                        "ransac_score": ts[1], "ransac_scored": ts[7], "V": V})
         return plane
 
+    # With several scans in flight the kernels of one scan at a time own the GPU (a host-side token), so that the
+    # lanes fall into a staggered schedule: one computes while the others copy.  Without it the lanes run in lock
+    # step, share the SMs, finish together and then all queue on PCIe with the GPU idle.
+    token = threading.Lock() if args.token else contextlib.nullcontext()
+
     def e2e_step(lane=None):
-        c, hi, ho = lane or (ctx, hin, hout)
+        c, hi, ho, hx = lane or (ctx, hin, hout, hinl)
         c.upload(nat.ATTR_POINTS, hi.array)            # H2D 24 B/point from page-locked memory
-        c.drop(nat.ATTR_NORMALS)
-        c.estimate_normals(nat.SEARCH_KNN, KNN, 0.0)
-        c.download_async(nat.ATTR_NORMALS, ho.array)   # D2H 24 B/point, on the copy stream while segment_plane runs
-        plane, inl = c.segment_plane(THR, RANSAC_N, ITERS, seed=1)   # D2H inliers + plane
+        if lane is None:                               # one scan at a time: the normals leave while segment_plane runs
+            c.drop(nat.ATTR_NORMALS)
+            c.estimate_normals(nat.SEARCH_KNN, KNN, 0.0)
+            c.download_async(nat.ATTR_NORMALS, ho.array)   # D2H 24 B/point on the copy stream
+            plane, inl = c.segment_plane(THR, RANSAC_N, ITERS, seed=1, inliers_out=hx.array)   # D2H inliers + plane
+        else:                                          # several in flight: the normals leave while the NEXT scan computes
+            c.synchronize()
+            with token:
+                c.drop(nat.ATTR_NORMALS)
+                c.estimate_normals(nat.SEARCH_KNN, KNN, 0.0)
+                plane, inl = c.segment_plane(THR, RANSAC_N, ITERS, seed=1, inliers_out=hx.array)
+                c.download_async(nat.ATTR_NORMALS, ho.array)
         c.synchronize()                                # normals complete on the host
         return plane, inl
 
@@ -226,12 +243,12 @@ def main():
     # the other.  Every step still uploads its own input and downloads its own normals, plane and inlier list.
     t_e2e = t_e2e_serial
     if args.inflight > 1:
-        lanes = [(ctx, hin, hout)]
+        lanes = [(ctx, hin, hout, hinl)]
         for _ in range(args.inflight - 1):
             c2 = nat.Context(local)
             hi2 = nat.PinnedArray((N, 3), np.float64)
             hi2.array[...] = pts
-            lanes.append((c2, hi2, nat.PinnedArray((N, 3), np.float64)))
+            lanes.append((c2, hi2, nat.PinnedArray((N, 3), np.float64), nat.PinnedArray((N,), np.int32)))
         for ln in lanes[1:]:
             e2e_step(ln)
         todo = list(range(args.steps))
@@ -255,9 +272,9 @@ def main():
             t.join()
         barrier()
         t_e2e = (time.perf_counter() - t0) * 1e3 / args.steps
-        for c2, hi2, ho2 in lanes[1:]:
+        for c2, hi2, ho2, hx2 in lanes[1:]:
             assert np.array_equal(ho2.array, hout.array), "pipelined normals differ from the serial result"
-            hi2.free(); ho2.free(); c2.close()
+            hi2.free(); ho2.free(); hx2.free(); c2.close()
     n_inl = int(len(inl))
 
     tm = torch.tensor([t_metric, t_step, t_e2e, t_e2e_serial], dtype=torch.float64, device=f"cuda:{local}")

@@ -145,7 +145,9 @@ static int download_async_impl(o3dpp_ctx *c, int attr, double *dst)
     if (n == 0) return 0;
     if (!dst) return set_err(O3DPP_E_ARG, "null destination");
     if (!c->copy_stream) {
-        CU_TRY(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+        int lo = 0, hi = 0;                                  // the interleave pass must not queue behind another scan's
+        CU_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi)); // 300 k-block neighbour search: highest priority
+        CU_TRY(cudaStreamCreateWithPriority(&c->copy_stream, cudaStreamNonBlocking, hi));
         CU_TRY(cudaEventCreateWithFlags(&c->copy_ev, cudaEventDisableTiming));
     }
     CU_TRY(cudaStreamSynchronize(c->copy_stream));          // stage2 may still feed an earlier copy

@@ -241,7 +241,9 @@ class Context:
         return idx, d2, cnt
 
     def segment_plane(self, distance_threshold, ransac_n, num_iterations, probability=0.99999999,
-                      sampler=SAMPLER_PHILOX, seed=0, samples=None, debug=False, fetch_inliers=True):
+                      sampler=SAMPLER_PHILOX, seed=0, samples=None, debug=False, fetch_inliers=True, inliers_out=None):
+        """inliers_out: optional caller-owned int32 buffer of >= n entries (e.g. page-locked) that receives the inlier list;
+        the returned array is then a view of its first n_inliers entries."""
         H = int(num_iterations)
         plane = np.zeros(4)
         best = np.zeros(4)
@@ -260,7 +262,12 @@ class Context:
                                          _ptr(plane), C.byref(m), _ptr(best), C.byref(bi), _ptr(counts), _ptr(errs)))
         inl = None
         if fetch_inliers:
-            inl = np.empty(m.value, np.int32)
+            if inliers_out is not None:
+                if inliers_out.dtype != np.int32 or not inliers_out.flags.c_contiguous or inliers_out.size < m.value:
+                    raise ValueError("inliers_out must be a contiguous int32 array with room for every inlier")
+                inl = inliers_out.reshape(-1)[:m.value]
+            else:
+                inl = np.empty(m.value, np.int32)
             if m.value:
                 _check(lib().o3dpp_fetch_inliers(self._h, _ptr(inl)))
         if debug:
