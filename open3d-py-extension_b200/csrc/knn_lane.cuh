@@ -25,7 +25,7 @@
 #define KL_WARPS 1
 #endif
 #ifndef KL_CAP
-#define KL_CAP 768      // staged candidates per warp
+#define KL_CAP 752      // staged candidates per warp (752 + KL_BND 22 + KL_LIST 56: eleven blocks per SM)
 #endif
 #ifndef KL_NB
 #define KL_NB 32        // histogram bins
@@ -58,7 +58,11 @@
 #define KL_WIN 2        // unstageable parts: cell groups taken before and after the home group along the curve
 #endif
 #ifndef KL_BND
-#define KL_BND 24       // boundary-bin list entries per query
+#define KL_BND 22       // boundary-bin list entries per query
+#endif
+
+#ifndef KL_LIST
+#define KL_LIST 56      // survivors of the threshold pass per query (16-bit staged slots): < K + KL_BND
 #endif
 
 struct KlWarpMem {
@@ -70,7 +74,7 @@ struct KlWarpMem {
         struct { float d[KL_BND * 32]; unsigned short s[KL_BND * 32]; } bnd; // [entry][lane]
     } u;
     union {
-        unsigned short nb[32 * 32];                                          // [j][lane] staged slots
+        unsigned short nb[KL_LIST * 32];                                     // [j][lane] staged slots: survivors, then the K neighbours
         unsigned gl[KL_GMAX];                                                // cell groups to scan (stage only)
     } v;
 };
@@ -92,6 +96,14 @@ __device__ __forceinline__ float2 kl_d2pair(const float4 a, const float4 b, floa
     float2 dx = __fadd2_rn(make_float2(a.x, a.y), nqx), dy = __fadd2_rn(make_float2(a.z, a.w), nqy),
            dz = __fadd2_rn(make_float2(b.x, b.y), nqz);
     return __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
+}
+
+// d2 of staged slot s, the same three roundings as the packed form
+__device__ __forceinline__ float kl_d2slot(const float4 *cand, int s, float qx, float qy, float qz)
+{
+    const float *r = (const float *)(cand + (s & ~1)) + (s & 1);
+    float dx = __fadd_rn(r[0], -qx), dy = __fadd_rn(r[2], -qy), dz = __fadd_rn(r[4], -qz);
+    return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
 }
 
 struct KlStage {
@@ -206,8 +218,13 @@ struct KlAnswer {
     unsigned why;     // 1 gap, 2 rho, 3 boundary overflow, 4 count, 5 not staged
 };
 
-// SELECT + CERTIFY of every lane's own query against the np staged candidates (np % 4 == 0).
-// T = histogram range (an upper bound of the k-th d2 of the staged set, or the hybrid radius cap).
+// SELECT + CERTIFY of every lane's own query against the np staged candidates (np % KL_UNR == 0).
+// U = an upper bound of the k-th d2 of the staged set (the histogram range; the hybrid radius cap if smaller).
+//   A  lane-private quarter-octave histogram of d2 over all candidates; b* = the bin that holds the k-th d2
+//   C  second pass: d2 below the upper edge of b* -> the slot joins the survivor list (16 bits each; c0 + cb <
+//      K + KL_BND entries), otherwise the smallest rejected d2 is tracked: one compare, one store per candidate
+//   F  the survivors are looked at again: bins below b* are neighbours (compacted in place), those of b* go to the
+//      boundary list and are ranked exactly; certification of the k-th against the (k+1)-th d2 and rho.
 template <int MODE>
 __device__ __forceinline__ KlAnswer kl_select(KlWarpMem &sm, int lane, int np, int K, float qx, float qy, float qz, float U,
                                               float tcap, float rho1f, float eA, float eC)
@@ -221,30 +238,23 @@ __device__ __forceinline__ KlAnswer kl_select(KlWarpMem &sm, int lane, int np, i
     const bool dead = !(T > 1e-36f);
     const int base = (__float_as_int(dead ? 1.0f : T) >> 21) - (KL_NB - 1);
     unsigned *hist = sm.u.hist + lane;
+    const float2 nqx = make_float2(-qx, -qx), nqy = make_float2(-qy, -qy), nqz = make_float2(-qz, -qz);
+    unsigned short *const list = sm.v.nb + lane;
 #pragma unroll
     for (int b = 0; b < KL_NB; ++b) hist[b * 32] = 0u;
-    // pass B: lane-private histogram of d2 (candidates are broadcast reads, loads issued ahead of the updates)
-    const float2 nqx = make_float2(-qx, -qx), nqy = make_float2(-qy, -qy), nqz = make_float2(-qz, -qz);
-    // the next KL_UNR candidates are loaded before the current ones are processed: the compiler cannot hoist
-    // the loads itself (the histogram atomics may alias the candidate array as far as it knows)
-    float4 nx[KL_UNR];
-#pragma unroll
-    for (int u = 0; u < KL_UNR; ++u) nx[u] = cd[u];
+    // pass A (candidates are broadcast reads; unconditional shared atomics, bin KL_NB = beyond the range)
     for (int s = 0; s < np; s += KL_UNR) {
         float4 cc[KL_UNR];
         int bb[KL_UNR];
 #pragma unroll
-        for (int u = 0; u < KL_UNR; ++u) { if (KL_PIPE) { cc[u] = nx[u]; nx[u] = cd[s + KL_UNR + u]; } else cc[u] = cd[s + u]; }   // reads past np are padded
+        for (int u = 0; u < KL_UNR; ++u) cc[u] = cd[s + u];
 #pragma unroll
         for (int u = 0; u < KL_UNR; u += 2) {
             float2 d = kl_d2pair(cc[u], cc[u + 1], nqx, nqy, nqz);
             bb[u] = kl_bin(d.x, base); bb[u + 1] = kl_bin(d.y, base);
         }
 #pragma unroll
-        for (int u = 0; u < KL_UNR; ++u) {
-            if (KL_ATOM) atomicAdd(hist + bb[u] * 32, 1u);
-            else hist[bb[u] * 32]++;
-        }
+        for (int u = 0; u < KL_UNR; ++u) atomicAdd(hist + bb[u] * 32, 1u);
     }
     int c0 = 0, bstar = -1, cb = 0, acc = 0;
 #pragma unroll
@@ -256,33 +266,40 @@ __device__ __forceinline__ KlAnswer kl_select(KlWarpMem &sm, int lane, int np, i
     const bool takeall = bstar < 0 && MODE == 2 && capped;   // fewer than K inside the radius
     const bool counted = bstar >= 0;
     if (takeall) bstar = KL_NB;
-    const int beq = (takeall || cb > KL_BND) ? -1 : bstar;   // a boundary bin too full for the list fails below
-    __syncwarp();     // the boundary lists alias the histograms of other lanes
-    // pass C: candidates below bin b* are neighbours (fewer than K of them), those inside it go to the
-    // boundary list (at most KL_BND), the smallest d2 above it is tracked
+    const bool fits = takeall || (counted && cb <= KL_BND);  // else: a boundary bin too full for the list fails below
+    const int beq = (takeall || !fits) ? -1 : bstar;
+    const int tb = fits ? ((takeall ? KL_NB : bstar + 1) + base) << 21 : 0;     // float bits of the upper edge of b*
+    // pass C
     float bmin = KF_HUGE;
-    float *bd = sm.u.bnd.d + lane, *bdp = bd;
-    unsigned short *bs = sm.u.bnd.s + lane, *bsp = bs, *nbp = sm.v.nb + lane;
-#pragma unroll
-    for (int u = 0; u < KL_UNR; ++u) nx[u] = cd[u];
+    int lo = 0;                                               // offset of the next free list entry
     for (int s = 0; s < np; s += KL_UNR) {
         float4 cc[KL_UNR];
         float dd[KL_UNR];
-        int bb[KL_UNR];
 #pragma unroll
-        for (int u = 0; u < KL_UNR; ++u) { if (KL_PIPE) { cc[u] = nx[u]; nx[u] = cd[s + KL_UNR + u]; } else cc[u] = cd[s + u]; }
+        for (int u = 0; u < KL_UNR; ++u) cc[u] = cd[s + u];
 #pragma unroll
         for (int u = 0; u < KL_UNR; u += 2) {
             float2 d = kl_d2pair(cc[u], cc[u + 1], nqx, nqy, nqz);
             dd[u] = d.x; dd[u + 1] = d.y;
-            bb[u] = kl_bin(d.x, base); bb[u + 1] = kl_bin(d.y, base);
         }
 #pragma unroll
         for (int u = 0; u < KL_UNR; ++u) {
-            if (bb[u] < bstar) { *nbp = (unsigned short)(s + u); nbp += 32; }
-            else if (bb[u] == beq) { *bdp = dd[u]; *bsp = (unsigned short)(s + u); bdp += 32; bsp += 32; }
+            if (__float_as_int(dd[u]) < tb) { list[lo] = (unsigned short)(s + u); lo = min(lo + 32, (KL_LIST - 1) * 32); }
             else bmin = fminf(bmin, dd[u]);
         }
+    }
+    const int live = lo >> 5;                                 // = c0 + cb (takeall: everything inside the range)
+    const int cmax = __reduce_max_sync(FULL, (unsigned)live);
+    __syncwarp();     // the boundary lists alias the histograms of other lanes
+    // pass F
+    float *bd = sm.u.bnd.d + lane, *bdp = bd;
+    unsigned short *bs = sm.u.bnd.s + lane, *bsp = bs, *nbp = list;
+    for (int e = 0; e < cmax; ++e) {
+        const int sl = e < live ? (int)list[e * 32] : 0;
+        const float d = kl_d2slot(cd, sl, qx, qy, qz);
+        const int b = e < live ? kl_bin(d, base) : KL_NB + 1;
+        if (b < bstar) { *nbp = (unsigned short)sl; nbp += 32; }
+        else if (b == beq) { *bdp = d; *bsp = (unsigned short)sl; bdp += 32; bsp += 32; }
     }
     const float ubound = U + kf_err(U, eA, eC) * 1.0001f;
     if (dead) { A.why = 4; A.capf = ubound; }
@@ -315,7 +332,7 @@ __device__ __forceinline__ KlAnswer kl_select(KlWarpMem &sm, int lane, int np, i
         A.capf = a + ea * 1.0001f;
         if (!c1) A.why = 1; else if (!c2) A.why = 2;
     }
-    A.cn = (int)(nbp - (sm.v.nb + lane)) >> 5;
+    A.cn = (int)(nbp - list) >> 5;
     return A;
 }
 
