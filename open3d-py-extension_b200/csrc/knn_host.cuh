@@ -37,7 +37,7 @@ static int launch_lane(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, c
     auto k1 = knn_lane_kernel<MODE>;
     CU_TRY(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int64_t blocks = (gd.cnt[0] + KL_WARPS - 1) / KL_WARPS;
-    float rho = 0.4f;          // staging radius / part-box diagonal (measured optimum on the LiDAR-like scans)
+    float rho = 0.44f;         // staging radius / part-box diagonal (measured optimum on the LiDAR-like scans)
     if (const char *e = getenv("O3DPP_KNN_RHO")) { float v = (float)atof(e); if (v > 0.f) rho = v; }
     // a part whose grown box overflows the staging area retries with the radius shrunk (x shrink, up to max_shrink
     // times), then is halved (never, at the default 12); gsplit = cell groups to scan beyond which an attempt is abandoned before scanning

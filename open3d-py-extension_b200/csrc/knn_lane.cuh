@@ -65,6 +65,8 @@
 #define KL_LIST 56      // survivors of the threshold pass per query (16-bit staged slots): < K + KL_BND
 #endif
 
+static_assert(32 - 1 + KL_BND < KL_LIST, "survivor list: K - 1 below the boundary bin + KL_BND inside it (K <= 32 on this path)");
+
 struct KlWarpMem {
     // candidates, two to a 32-byte record {x0 x1 y0 y1 | z0 z1 p0 p1} so that the select passes run on packed
     // FP32 pairs (FFMA2); p = sorted position bits
@@ -105,6 +107,10 @@ __device__ __forceinline__ float kl_d2slot(const float4 *cand, int s, float qx, 
     float dx = __fadd_rn(r[0], -qx), dy = __fadd_rn(r[2], -qy), dz = __fadd_rn(r[4], -qz);
     return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
 }
+
+// stores through 32-bit shared addresses: a running generic pointer costs a 64-bit add per step
+__device__ __forceinline__ void kl_sts16(unsigned a, unsigned short v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"(v) : "memory"); }
+__device__ __forceinline__ void kl_sts32(unsigned a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
 
 struct KlStage {
     const GridDesc &g;
@@ -269,9 +275,10 @@ __device__ __forceinline__ KlAnswer kl_select(KlWarpMem &sm, int lane, int np, i
     const bool fits = takeall || (counted && cb <= KL_BND);  // else: a boundary bin too full for the list fails below
     const int beq = (takeall || !fits) ? -1 : bstar;
     const int tb = fits ? ((takeall ? KL_NB : bstar + 1) + base) << 21 : 0;     // float bits of the upper edge of b*
-    // pass C
-    float bmin = KF_HUGE;
-    int lo = 0;                                               // offset of the next free list entry
+    // pass C: the histogram guarantees c0 + cb < K + KL_BND <= KL_LIST survivors, so the list cannot overflow; every
+    // rejected d2 is >= tau (the upper edge of b*), which is all the certification needs to know about them
+    const unsigned la0 = (unsigned)__cvta_generic_to_shared(list);   // 32-bit shared address: one add per survivor
+    unsigned la = la0;
     for (int s = 0; s < np; s += KL_UNR) {
         float4 cc[KL_UNR];
         float dd[KL_UNR];
@@ -283,23 +290,25 @@ __device__ __forceinline__ KlAnswer kl_select(KlWarpMem &sm, int lane, int np, i
             dd[u] = d.x; dd[u + 1] = d.y;
         }
 #pragma unroll
-        for (int u = 0; u < KL_UNR; ++u) {
-            if (__float_as_int(dd[u]) < tb) { list[lo] = (unsigned short)(s + u); lo = min(lo + 32, (KL_LIST - 1) * 32); }
-            else bmin = fminf(bmin, dd[u]);
-        }
+        for (int u = 0; u < KL_UNR; ++u)
+            if (__float_as_int(dd[u]) < tb) {
+                kl_sts16(la, (unsigned short)(s + u));
+                la += 64;
+            }
     }
-    const int live = lo >> 5;                                 // = c0 + cb (takeall: everything inside the range)
+    const int live = (int)(la - la0) >> 6;                    // = c0 + cb (takeall: everything inside the range)
     const int cmax = __reduce_max_sync(FULL, (unsigned)live);
     __syncwarp();     // the boundary lists alias the histograms of other lanes
     // pass F
-    float *bd = sm.u.bnd.d + lane, *bdp = bd;
-    unsigned short *bs = sm.u.bnd.s + lane, *bsp = bs, *nbp = list;
+    float *bd = sm.u.bnd.d + lane;
+    unsigned short *bs = sm.u.bnd.s + lane;
+    unsigned bda = (unsigned)__cvta_generic_to_shared(bd), bsa = (unsigned)__cvta_generic_to_shared(bs), nba = la0;
     for (int e = 0; e < cmax; ++e) {
         const int sl = e < live ? (int)list[e * 32] : 0;
         const float d = kl_d2slot(cd, sl, qx, qy, qz);
         const int b = e < live ? kl_bin(d, base) : KL_NB + 1;
-        if (b < bstar) { *nbp = (unsigned short)sl; nbp += 32; }
-        else if (b == beq) { *bdp = d; *bsp = (unsigned short)sl; bdp += 32; bsp += 32; }
+        if (b < bstar) { kl_sts16(nba, (unsigned short)sl); nba += 64; }
+        else if (b == beq) { kl_sts32(bda, d); kl_sts16(bsa, (unsigned short)sl); bda += 128; bsa += 64; }
     }
     const float ubound = U + kf_err(U, eA, eC) * 1.0001f;
     if (dead) { A.why = 4; A.capf = ubound; }
@@ -320,11 +329,11 @@ __device__ __forceinline__ KlAnswer kl_select(KlWarpMem &sm, int lane, int np, i
             int be = 0;
             for (int e = 0; e < cb; ++e) { float v = bd[e * 32]; if (v < best) { best = v; be = e; } }
             a = best;
-            *nbp = bs[be * 32];
-            nbp += 32;
+            kl_sts16(nba, bs[be * 32]);
+            nba += 64;
             bd[be * 32] = KF_HUGE;
         }
-        float rest = bmin;
+        float rest = __int_as_float(tb);                            // tau: no rejected candidate is closer
         for (int e = 0; e < cb; ++e) rest = fminf(rest, bd[e * 32]);
         const float ea = kf_err(a, eA, eC);
         const bool c1 = rest - a > 2.0f * kf_err(rest, eA, eC), c2 = a + ea <= rho1f;
@@ -332,7 +341,7 @@ __device__ __forceinline__ KlAnswer kl_select(KlWarpMem &sm, int lane, int np, i
         A.capf = a + ea * 1.0001f;
         if (!c1) A.why = 1; else if (!c2) A.why = 2;
     }
-    A.cn = (int)(nbp - list) >> 5;
+    A.cn = (int)(nba - la0) >> 6;
     return A;
 }
 
