@@ -46,11 +46,38 @@ def peaks():
 
 
 class ClockSampler:
+    """SM clock and throttle reasons of one GPU sampled DURING the timed region: NVML from a thread every 5 ms
+    (the timed region of the device leg is ~0.1 s), `nvidia-smi -lms` as the fallback."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    BITS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
 
-    def __init__(self, index):
-        self.rows, self.proc = [], None
+    def __init__(self, index, uuid=None):
+        self.rows, self.proc, self.nv, self.h, self.mx = [], None, None, None, None
+        self.alive = True
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = None
+            if uuid:
+                try:
+                    h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(uuid)) if not str(uuid).startswith("GPU-") else str(uuid))
+                except Exception:
+                    h = None
+            if h is None:
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+                phys = index
+                if vis:
+                    ent = vis.split(",")[index].strip()
+                    phys = int(ent) if ent.isdigit() else index
+                h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            self.nv, self.h = pynvml, h
+            self.t = threading.Thread(target=self._poll, daemon=True)
+            self.t.start()
+            return
+        except Exception:
+            self.nv = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
                                           "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -59,11 +86,33 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def _poll(self):
+        nv = self.nv
+        reasons_of = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        while self.alive:
+            try:
+                mhz = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                mask = int(reasons_of(self.h))
+                self.rows.append((time.time(), mhz, mask))
+            except Exception:
+                pass
+            time.sleep(0.005)
+
     def _pump(self):
         for line in self.proc.stdout:
             self.rows.append((time.time(), line.strip()))
 
     def stop(self, t0, t1):
+        if self.nv is not None:
+            time.sleep(0.02)
+            self.alive = False
+            sm = [r[1] for r in self.rows if t0 - 0.01 <= r[0] <= t1 + 0.01]
+            mask = 0
+            for r in self.rows:
+                if t0 - 0.01 <= r[0] <= t1 + 0.01:
+                    mask |= r[2]
+            return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.mx,
+                    "reasons": sorted(k for k, b in self.BITS.items() if mask & b), "samples": len(sm), "source": "nvml"}
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -84,7 +133,33 @@ class ClockSampler:
             except ValueError:
                 continue
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "source": "nvidia-smi"}
+
+
+def bind_to_gpu_numa_node(index):
+    """Several ranks on one host: run this process (and place its page-locked buffers, first touch) on the CPUs of the
+    NUMA node its GPU hangs off, so that the 0.5 GB of copies per step do not cross the socket interconnect.
+    Returns the node number, or None when the topology is not visible (nothing is changed then)."""
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(index).pci_bus_id
+        dom = getattr(torch.cuda.get_device_properties(index), "pci_domain_id", 0)
+        dev = getattr(torch.cuda.get_device_properties(index), "pci_device_id", 0)
+        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev:02x}.0/numa_node"
+        node = int(open(path).read().strip())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = os.sched_getaffinity(0) & cpus
+        if len(allowed) < 2:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return node
+    except Exception:
+        return None
 
 
 def oracle_pass(pts, threads):
@@ -161,6 +236,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    numa = bind_to_gpu_numa_node(local) if world > 1 else None   # before the page-locked buffers are allocated
     N = args.points
     pts = lidar_like(N, SEED_C3 + rank)          # every rank owns its own scan
     ctx = nat.Context(local)
@@ -217,7 +293,7 @@ def main():
     for _ in range(args.warmup):
         device_step(scratch)
     barrier()
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(local, getattr(torch.cuda.get_device_properties(local), "uuid", None))
     l0 = ctx.launch_count()
     stages = []
     wall0 = time.time()
@@ -295,7 +371,8 @@ def main():
                                    " (voxel_down_sample(0.1) timed beside it)",
                        "points_per_gpu": N, "sharding": "one scan per GPU, no data-path collective",
                        "l2": "inputs (240 MB FP64 planes per scan) exceed the 126 MB L2",
-                       "timing": "CUDA events on the library stream; max over ranks"},
+                       "timing": "CUDA events on the library stream; max over ranks",
+                       "numa_node_of_rank0": numa},
             "stages_ms": med, "chain_ms_per_step": t_step,
             "e2e": {"value": world * N / (t_e2e * 1e-3) / 1e6, "unit": "Mpoints/s", "ms_per_step": t_e2e,
                     "scans_in_flight": args.inflight, "serial_value": world * N / (t_e2e_serial * 1e-3) / 1e6,

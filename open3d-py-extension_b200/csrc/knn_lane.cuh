@@ -628,17 +628,27 @@ struct K2Range {
         bool ex = c < g.cnt[LVL];
         float lb = ex ? kl_box_lb(g, LVL, c, fql[0], fqh[0], fql[1], fqh[1], fql[2], fqh[2]) : KF_HUGE;
         unsigned m = __ballot_sync(FULL, ex && lb <= capf);
-        // nearest child first: the bound drops early (shrink) and the far children are never opened
-        const unsigned key = __float_as_uint(lb);
-        while (m && (K2_SHRINK || cnt <= K2_LIST)) {
-            m &= __ballot_sync(FULL, lb <= capf);     // the bound may have dropped
-            if (!m) break;
-            const bool mine = (m >> lane) & 1u;
-            const unsigned kmin = __reduce_min_sync(FULL, mine ? key : 0xffffffffu);
-            int b = __ffs(__ballot_sync(FULL, mine && key == kmin)) - 1;
-            m &= ~(1u << b);
-            if constexpr (LVL == 0) leaf(parent * 32 + b);
-            else visit<LVL - 1>(parent * 32 + b);
+        if constexpr (!K2_SHRINK) {
+            // fixed bound: every child that intersects the ball is opened, the order does not matter
+            while (m && cnt <= K2_LIST) {
+                const int b = __ffs(m) - 1;
+                m &= m - 1;
+                if constexpr (LVL == 0) leaf(parent * 32 + b);
+                else visit<LVL - 1>(parent * 32 + b);
+            }
+        } else {
+            // nearest child first: the bound drops early (shrink) and the far children are never opened
+            const unsigned key = __float_as_uint(lb);
+            while (m) {
+                m &= __ballot_sync(FULL, lb <= capf);     // the bound may have dropped
+                if (!m) break;
+                const bool mine = (m >> lane) & 1u;
+                const unsigned kmin = __reduce_min_sync(FULL, mine ? key : 0xffffffffu);
+                int b = __ffs(__ballot_sync(FULL, mine && key == kmin)) - 1;
+                m &= ~(1u << b);
+                if constexpr (LVL == 0) leaf(parent * 32 + b);
+                else visit<LVL - 1>(parent * 32 + b);
+            }
         }
     }
 
