@@ -112,7 +112,7 @@ __device__ __forceinline__ double plane_dist(double a, double b, double c, doubl
 
 __global__ void __launch_bounds__(SC_THREADS)
 score_kernel(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z, int64_t n,
-             const double *__restrict__ planes, int h0, int H, double thr,
+             const double *__restrict__ planes, int h0, int H, int hper /* hypotheses per blockIdx.y, <= SC_HB */, double thr,
              unsigned long long *__restrict__ part_cnt /*[gridDim.x][Hbatch]*/, double *__restrict__ part_err)
 {
     extern __shared__ unsigned char sc_smem[];
@@ -120,8 +120,8 @@ score_kernel(const double *__restrict__ x, const double *__restrict__ y, const d
     uint32_t *scnt = (uint32_t *)(sc_smem + SC_HB * SC_THREADS * 8);     // [SC_HB][SC_THREADS]
     __shared__ double spl[SC_HB][4];
     const int tid = threadIdx.x;
-    const int hbase = h0 + blockIdx.y * SC_HB;
-    const int nh = H - hbase < SC_HB ? H - hbase : SC_HB;
+    const int hbase = h0 + blockIdx.y * hper;
+    const int nh = H - hbase < hper ? (H - hbase > 0 ? H - hbase : 0) : hper;
     if (tid < SC_HB * 4) {
         int hh = tid >> 2;
         spl[hh][tid & 3] = hh < nh ? planes[4 * (hbase + hh) + (tid & 3)] : 0.0;
@@ -181,15 +181,16 @@ score_kernel(const double *__restrict__ x, const double *__restrict__ y, const d
 
 // sum the per-block partials in block order
 __global__ void score_final_kernel(const unsigned long long *__restrict__ part_cnt, const double *__restrict__ part_err,
-                                   int blocks, int Hb, long long *__restrict__ cnt, double *__restrict__ err)
+                                   int blocks, int Hb, int per, long long *__restrict__ cnt, double *__restrict__ err)
 {
     int h = blockIdx.x * blockDim.x + threadIdx.x;
-    if (h >= Hb) return;
+    if (h >= Hb || h % SC_HB >= per) return;
     unsigned long long c = 0;
     double e = 0.0;
     for (int b = 0; b < blocks; ++b) { c += part_cnt[(int64_t)b * Hb + h]; e = __dadd_rn(e, part_err[(int64_t)b * Hb + h]); }
-    cnt[h] = (long long)c;
-    err[h] = e;
+    const int o = (h / SC_HB) * per + h % SC_HB;        // columns of a chunk are packed `per` to a block row
+    cnt[o] = (long long)c;
+    err[o] = e;
 }
 
 struct PlanePred {
@@ -310,14 +311,18 @@ static int segment_plane_impl(o3dpp_ctx *c, double thr, int rn, int H, double pr
     if (counts_out) for (int h = 0; h < H; ++h) { counts_out[h] = -1; if (errs_out) errs_out[h] = 0.0; }
     long long hc[BATCH];
     double he[BATCH];
-    for (int h0 = 0; h0 < H; h0 += BATCH) {
+    for (int h0 = 0, hb = 0; h0 < H; h0 += hb) {
         if ((double)iteration_count > break_iteration) break;
-        int hb = H - h0 < BATCH ? H - h0 : BATCH;
+        hb = H - h0 < BATCH ? H - h0 : BATCH;
+        // the serial loop stops after iteration break_iteration: do not score past it (the bound only ever drops)
+        const double left = break_iteration + 1.0 - (double)iteration_count;
+        if (left < (double)hb) hb = left < 1.0 ? 1 : (int)left;
         int gy = (hb + SC_HB - 1) / SC_HB;
+        const int per = (hb + gy - 1) / gy;                 // even split: the blocks of a wave finish together
         dim3 grid(gx, gy);
-        score_kernel<<<grid, SC_THREADS, smem, c->stream>>>(X, Y, Z, n, c->r_planes.as<double>(), h0, H, thr, pc, pe);
+        score_kernel<<<grid, SC_THREADS, smem, c->stream>>>(X, Y, Z, n, c->r_planes.as<double>(), h0, h0 + hb, per, thr, pc, pe);
         c->launches++;
-        LAUNCH(c, score_final_kernel, 1, 64, 0, pc, pe, gx, gy * SC_HB, c->r_cnt.as<long long>(), c->r_err.as<double>());
+        LAUNCH(c, score_final_kernel, 1, 64, 0, pc, pe, gx, gy * SC_HB, per, c->r_cnt.as<long long>(), c->r_err.as<double>());
         O3_TRY(check_launch("score"));
         CU_TRY(cudaMemcpyAsync(hc, c->r_cnt.p, hb * 8, cudaMemcpyDeviceToHost, c->stream));
         CU_TRY(cudaMemcpyAsync(he, c->r_err.p, hb * 8, cudaMemcpyDeviceToHost, c->stream));

@@ -79,9 +79,9 @@ static int score_planes_impl(o3dpp_ctx *c, const double *planes, int H, double t
         int hb = H - h0 < BATCH ? H - h0 : BATCH;
         int gy = (hb + SC_HB - 1) / SC_HB;
         dim3 grid(gx, gy);
-        score_kernel<<<grid, SC_THREADS, smem, c->stream>>>(X, Y, Z, n, c->r_planes.as<double>(), h0, H, thr, pc, pe);
+        score_kernel<<<grid, SC_THREADS, smem, c->stream>>>(X, Y, Z, n, c->r_planes.as<double>(), h0, H, SC_HB, thr, pc, pe);
         c->launches++;
-        LAUNCH(c, score_final_kernel, 1, 64, 0, pc, pe, gx, gy * SC_HB, c->r_cnt.as<long long>() + h0, c->r_err.as<double>() + h0);
+        LAUNCH(c, score_final_kernel, 1, 64, 0, pc, pe, gx, gy * SC_HB, SC_HB, c->r_cnt.as<long long>() + h0, c->r_err.as<double>() + h0);
     }
     O3_TRY(check_launch("score_planes"));
     cudaEventRecord(c->ev[1], c->stream);

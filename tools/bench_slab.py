@@ -10,6 +10,8 @@ import argparse, json, os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "open3d-py-extension_b200"))
 import numpy as np
+if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+    os.environ["NCCL_DEBUG"] = "WARN"      # NCCL's version banner goes to stdout: keep the JSON line alone there
 import torch
 import torch.distributed as dist
 from open3dpypro import _native as nat
