@@ -217,8 +217,11 @@ __device__ __forceinline__ void eig_vec1(const double *A, const double *e0, doub
     }
 }
 
-__device__ __forceinline__ void fast_eigen3x3(const double *C, double *out)
+// sep (optional): distance between the two smallest eigenvalues in units of the largest coefficient of C, i.e. how
+// well the returned direction is determined (0 when C is zero)
+__device__ __forceinline__ void fast_eigen3x3(const double *C, double *out, double *sep = nullptr)
 {
+    if (sep) *sep = 0.0;
     double mc = C[0];
 #pragma unroll
     for (int a = 1; a < 6; ++a) if (C[a] > mc) mc = C[a];
@@ -244,6 +247,10 @@ __device__ __forceinline__ void fast_eigen3x3(const double *C, double *out)
         double beta0 = cos(angle + two_thirds_pi) * 2.0;
         double beta1 = -(beta0 + beta2);
         double e0 = q + p * beta0, e1 = q + p * beta1, e2 = q + p * beta2;
+        if (sep) {
+            const double lo = fmin(e0, fmin(e1, e2)), hi = fmax(e0, fmax(e1, e2));
+            *sep = ((e0 + e1 + e2) - lo - hi) - lo;
+        }
         double v0[3], v1[3], v2[3];
         if (half_det >= 0.0) {
             eig_vec0(A, e2, v2);
@@ -261,6 +268,10 @@ __device__ __forceinline__ void fast_eigen3x3(const double *C, double *out)
             out[0] = v2[0]; out[1] = v2[1]; out[2] = v2[2];
         }
     } else {
+        if (sep) {
+            const double lo = fmin(A[0], fmin(A[3], A[5])), hi = fmax(A[0], fmax(A[3], A[5]));
+            *sep = ((A[0] + A[3] + A[5]) - lo - hi) - lo;
+        }
         if (C[0] < C[3] && C[0] < C[5]) { out[0] = 1; out[1] = 0; out[2] = 0; }
         else if (C[3] < C[0] && C[3] < C[5]) { out[0] = 0; out[1] = 1; out[2] = 0; }
         else { out[0] = 0; out[1] = 0; out[2] = 1; }

@@ -122,13 +122,26 @@ struct KfStage {
     }
 };
 
-// covariance -> normal -> sign alignment -> store (Open3D EstimateNormals tail)
-__device__ __forceinline__ void kf_store_normal(const Cumul &cu, uint32_t qo, const KnnOut &out)
+// covariance -> normal -> sign alignment -> store (Open3D EstimateNormals tail).
+// guard = the cumulants were NOT summed in the reference's order (neighbours by increasing (d2, index)).  Open3D's
+// one-pass covariance E[ab] - E[a]E[b] cancels |mean|^2 against the variance; when that cancellation times the
+// FP64 rounding of a 30-term sum, divided by the eigenvalue separation, could move the direction by more than
+// 1e-5 rad, the result depends on the summation order: nothing is stored, false is returned and the caller leaves
+// the query to the exact tier, which replays the reference's order.
+__device__ __forceinline__ bool kf_store_normal(const Cumul &cu, uint32_t qo, const KnnOut &out, bool guard = false)
 {
     double C[6];
     cu.cov(C);
-    double nv[3];
-    fast_eigen3x3(C, nv);
+    double nv[3], sep = 0.0;
+    fast_eigen3x3(C, nv, guard ? &sep : nullptr);
+    if (guard && cu.n >= 3) {
+        const double dn = (double)cu.n, m0 = cu.c[0] / dn, m1 = cu.c[1] / dn, m2 = cu.c[2] / dn;
+        const double mm = fmax(m0 * m0, fmax(m1 * m1, m2 * m2));
+        double mc = C[0];
+#pragma unroll
+        for (int a = 1; a < 6; ++a) mc = fmax(mc, C[a]);
+        if (2e-15 * mm > 1e-5 * sep * mc) return false;
+    }
     double nn = sqrt((nv[0] * nv[0] + nv[1] * nv[1]) + nv[2] * nv[2]);
     double ox = 0, oy = 0, oz = 0;
     if (out.has_old_normals) { ox = out.nx[qo]; oy = out.ny[qo]; oz = out.nz[qo]; }
@@ -138,6 +151,7 @@ __device__ __forceinline__ void kf_store_normal(const Cumul &cu, uint32_t qo, co
     }
     if (out.has_old_normals && ((nv[0] * ox + nv[1] * oy) + nv[2] * oz) < 0.0) { nv[0] = -nv[0]; nv[1] = -nv[1]; nv[2] = -nv[2]; }
     out.nx[qo] = nv[0]; out.ny[qo] = nv[1]; out.nz[qo] = nv[2];
+    return true;
 }
 
 // exact answer of one query by the FP64 range-table search (the certified path's fallback), finished

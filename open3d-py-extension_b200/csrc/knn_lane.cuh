@@ -476,7 +476,7 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, int max
             if (window) { A.ok = false; A.why = 5; }      // rho1f < 0 already refuses; the bound A.capf is what counts
         } else if (nq >= K) A.capf = U + kf_err(U, eA, eC) * 1.0001f;
         if (inpart && valid) {
-            capbuf[mypos] = A.ok ? -fmaxf(A.capf, 1e-30f) : A.capf;   // negative = answered, magnitude bounds the k-th d2
+            bool answered = A.ok;
             if (out.stats) { n1 += A.why == 1; n2 += A.why == 2; n3 += A.why == 3; n4 += A.why == 4; n5 += A.why == 5; }
             if (A.ok && out.nx) {
                 Cumul cu;
@@ -497,8 +497,9 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, int max
                         cu.add(x[u], y[u], z[u]);
                     }
                 }
-                kf_store_normal(cu, g.sidx[mypos], out);
+                answered = kf_store_normal(cu, g.sidx[mypos], out, true);   // false: order-sensitive covariance, exact tier
             }
+            capbuf[mypos] = answered ? -fmaxf(A.capf, 1e-30f) : A.capf;   // negative = answered, magnitude bounds the k-th d2
         }
         __syncwarp();
         start += len;
@@ -740,8 +741,9 @@ knn_range_kernel(const GridDesc g, int K, double radius, KnnOut out, const int32
         __syncwarp();
     }
     if (!done) return;
-    capbuf[myq] = -fmaxf(__double2float_ru(mykth), 1e-30f);
-    if (out.nx) kf_store_normal(mine, g.sidx[myq], out);
+    const float kb = fmaxf(__double2float_ru(mykth), 1e-30f);
+    const bool stored = out.nx ? kf_store_normal(mine, g.sidx[myq], out, true) : true;
+    capbuf[myq] = stored ? -kb : kb;       // order-sensitive covariance: stays pending for the exact tier, with its bound
 }
 
 

@@ -240,6 +240,30 @@ def test_normals_lidar_200k(ctx, orc):
     _check_normals(ctx, orc, lidar_like(200_000, 78), 2, 30, 0.5)
 
 
+def _adversarial(n_each=40_000, seed=21, offset=0.0):
+    """what breaks a grid: uniform volume + duplicated surface points + tight clusters far apart + an exact lattice
+    (d2 ties) + a few far outliers, shuffled"""
+    rng = np.random.default_rng(seed)
+    vol = rng.uniform(-20, 20, size=(n_each, 3))
+    surf = np.concatenate([rng.uniform(-30, 30, size=(n_each // 4, 2)), np.zeros((n_each // 4, 1))], 1)
+    surf = np.repeat(surf, 4, axis=0)                                                   # every point four times
+    cen = rng.uniform(-50, 50, size=(40, 3))
+    clus = cen[rng.integers(0, 40, n_each)] + rng.normal(scale=1e-3, size=(n_each, 3))  # 1 mm clusters, 100 m apart
+    g = np.arange(34, dtype=np.float64) * 0.25
+    lat = np.stack(np.meshgrid(g, g, g, indexing="ij"), -1).reshape(-1, 3) + 60.0       # 39 304 lattice points
+    far = rng.uniform(-1000, 1000, size=(50, 3))
+    pts = np.concatenate([vol, surf, clus, lat, far], 0) + offset
+    return pts[rng.permutation(len(pts))]
+
+
+def test_knn_and_normals_adversarial(ctx, orc):
+    pts = _adversarial()
+    _check_knn(ctx, orc, pts[::4], 30)                 # index sets incl. exact ties, list kernel
+    _check_normals(ctx, orc, pts, 0, 30, 0.0, exact=False)           # tier chain
+    _check_normals(ctx, orc, pts, 2, 30, 0.3, exact=False)
+    _check_normals(ctx, orc, _adversarial(10_000, 22, offset=5000.0), 0, 30, 0.0, exact=False)   # large coordinates
+
+
 # ------------------------------------------------------------------ segment_plane
 def _check_segment(ctx, orc, pts, thr, rn, H, seed=7, prob=0.99999999):
     ctx.upload(nat.ATTR_POINTS, pts)
