@@ -247,10 +247,7 @@ __device__ __forceinline__ void fast_eigen3x3(const double *C, double *out, doub
         double beta0 = cos(angle + two_thirds_pi) * 2.0;
         double beta1 = -(beta0 + beta2);
         double e0 = q + p * beta0, e1 = q + p * beta1, e2 = q + p * beta2;
-        if (sep) {
-            const double lo = fmin(e0, fmin(e1, e2)), hi = fmax(e0, fmax(e1, e2));
-            *sep = ((e0 + e1 + e2) - lo - hi) - lo;
-        }
+        if (sep) *sep = p * (beta1 - beta0);      // angle in [0, pi/3]: beta0 <= beta1 <= beta2, so e0 <= e1 <= e2
         double v0[3], v1[3], v2[3];
         if (half_det >= 0.0) {
             eig_vec0(A, e2, v2);

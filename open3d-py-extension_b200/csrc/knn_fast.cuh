@@ -135,12 +135,12 @@ __device__ __forceinline__ bool kf_store_normal(const Cumul &cu, uint32_t qo, co
     double nv[3], sep = 0.0;
     fast_eigen3x3(C, nv, guard ? &sep : nullptr);
     if (guard && cu.n >= 3) {
-        const double dn = (double)cu.n, m0 = cu.c[0] / dn, m1 = cu.c[1] / dn, m2 = cu.c[2] / dn;
-        const double mm = fmax(m0 * m0, fmax(m1 * m1, m2 * m2));
+        const double dn = (double)cu.n;
+        const double ss = fmax(cu.c[0] * cu.c[0], fmax(cu.c[1] * cu.c[1], cu.c[2] * cu.c[2]));   // (n * largest |mean|)^2
         double mc = C[0];
 #pragma unroll
         for (int a = 1; a < 6; ++a) mc = fmax(mc, C[a]);
-        if (2e-15 * mm > 1e-5 * sep * mc) return false;
+        if (2e-15 * ss > (1e-5 * sep) * (mc * (dn * dn))) return false;
     }
     double nn = sqrt((nv[0] * nv[0] + nv[1] * nv[1]) + nv[2] * nv[2]);
     double ox = 0, oy = 0, oz = 0;

@@ -61,6 +61,9 @@
 #define KL_BND 22       // boundary-bin list entries per query
 #endif
 
+#ifndef KL_GUARD
+#define KL_GUARD true   // order-sensitivity guard of the covariance (kf_store_normal); false only for A/B timing
+#endif
 #ifndef KL_LIST
 #define KL_LIST 56      // survivors of the threshold pass per query (16-bit staged slots): < K + KL_BND
 #endif
@@ -497,7 +500,7 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, int max
                         cu.add(x[u], y[u], z[u]);
                     }
                 }
-                answered = kf_store_normal(cu, g.sidx[mypos], out, true);   // false: order-sensitive covariance, exact tier
+                answered = kf_store_normal(cu, g.sidx[mypos], out, KL_GUARD);   // false: order-sensitive covariance, exact tier
             }
             capbuf[mypos] = answered ? -fmaxf(A.capf, 1e-30f) : A.capf;   // negative = answered, magnitude bounds the k-th d2
         }
@@ -742,7 +745,7 @@ knn_range_kernel(const GridDesc g, int K, double radius, KnnOut out, const int32
     }
     if (!done) return;
     const float kb = fmaxf(__double2float_ru(mykth), 1e-30f);
-    const bool stored = out.nx ? kf_store_normal(mine, g.sidx[myq], out, true) : true;
+    const bool stored = out.nx ? kf_store_normal(mine, g.sidx[myq], out, KL_GUARD) : true;
     capbuf[myq] = stored ? -kb : kb;       // order-sensitive covariance: stays pending for the exact tier, with its bound
 }
 
