@@ -1,3 +1,5 @@
+"""Diagnostic: worst normal-angle offenders of the tier chain against the oracle on the adversarial cloud of
+tests/test_gpu_parity.py (O3DPP_KNN_LIST=1 runs the reference-order list kernel instead)."""
 import sys, os
 sys.path.insert(0, 'open3d-py-extension_b200'); sys.path.insert(0, '.'); sys.path.insert(0, 'tests')
 import numpy as np
