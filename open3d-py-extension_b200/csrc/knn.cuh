@@ -161,6 +161,19 @@ __device__ __forceinline__ void cross3d(const double *a, const double *b, double
 }
 __device__ __forceinline__ double dot3d(const double *a, const double *b) { return (a[0] * b[0] + a[1] * b[1]) + a[2] * b[2]; }
 
+// FP64 division and square root out of line (IEEE results, same bits as the inline expansion): the normal solve has
+// ~30 of them at ~25 instructions each, and the kernels that finish queries are bound by instruction fetch
+#ifndef O3_NIDIV
+#define O3_NIDIV 1
+#endif
+#if O3_NIDIV
+__device__ __noinline__ double o3_div(double a, double b) { return a / b; }
+__device__ __noinline__ double o3_sqrt(double a) { return sqrt(a); }
+#else
+__device__ __forceinline__ double o3_div(double a, double b) { return a / b; }
+__device__ __forceinline__ double o3_sqrt(double a) { return sqrt(a); }
+#endif
+
 __device__ __forceinline__ void eig_vec0(const double *A, double ev, double *out)
 {
     double r0[3] = {A[0] - ev, A[1], A[2]};
@@ -177,18 +190,18 @@ __device__ __forceinline__ void eig_vec0(const double *A, double ev, double *out
     double sy = imax == 0 ? x01[1] : (imax == 1 ? x02[1] : x12[1]);
     double sz = imax == 0 ? x01[2] : (imax == 1 ? x02[2] : x12[2]);
     double dd = imax == 0 ? d0 : (imax == 1 ? d1 : d2);
-    double s = sqrt(dd);
-    out[0] = sx / s; out[1] = sy / s; out[2] = sz / s;
+    double s = o3_sqrt(dd);
+    out[0] = o3_div(sx, s); out[1] = o3_div(sy, s); out[2] = o3_div(sz, s);
 }
 
 __device__ __forceinline__ void eig_vec1(const double *A, const double *e0, double ev1, double *out)
 {
     double U[3], V[3];
     if (fabs(e0[0]) > fabs(e0[1])) {
-        double il = 1.0 / sqrt(e0[0] * e0[0] + e0[2] * e0[2]);
+        double il = o3_div(1.0, o3_sqrt(e0[0] * e0[0] + e0[2] * e0[2]));
         U[0] = -e0[2] * il; U[1] = 0.0; U[2] = e0[0] * il;
     } else {
-        double il = 1.0 / sqrt(e0[1] * e0[1] + e0[2] * e0[2]);
+        double il = o3_div(1.0, o3_sqrt(e0[1] * e0[1] + e0[2] * e0[2]));
         U[0] = 0.0; U[1] = e0[2] * il; U[2] = -e0[1] * il;
     }
     cross3d(e0, U, V);
@@ -203,15 +216,15 @@ __device__ __forceinline__ void eig_vec1(const double *A, const double *e0, doub
     if (a00 >= a11) {
         double mx = a00 > a01 ? a00 : a01;
         if (mx > 0) {
-            if (a00 >= a01) { m01 /= m00; m00 = 1.0 / sqrt(1.0 + m01 * m01); m01 *= m00; }
-            else            { m00 /= m01; m01 = 1.0 / sqrt(1.0 + m00 * m00); m00 *= m01; }
+            if (a00 >= a01) { m01 = o3_div(m01, m00); m00 = o3_div(1.0, o3_sqrt(1.0 + m01 * m01)); m01 *= m00; }
+            else            { m00 = o3_div(m00, m01); m01 = o3_div(1.0, o3_sqrt(1.0 + m00 * m00)); m00 *= m01; }
             for (int a = 0; a < 3; ++a) out[a] = m01 * U[a] - m00 * V[a];
         } else { for (int a = 0; a < 3; ++a) out[a] = U[a]; }
     } else {
         double mx = a11 > a01 ? a11 : a01;
         if (mx > 0) {
-            if (a11 >= a01) { m01 /= m11; m11 = 1.0 / sqrt(1.0 + m01 * m01); m01 *= m11; }
-            else            { m11 /= m01; m01 = 1.0 / sqrt(1.0 + m11 * m11); m11 *= m01; }
+            if (a11 >= a01) { m01 = o3_div(m01, m11); m11 = o3_div(1.0, o3_sqrt(1.0 + m01 * m01)); m01 *= m11; }
+            else            { m11 = o3_div(m11, m01); m01 = o3_div(1.0, o3_sqrt(1.0 + m11 * m11)); m11 *= m01; }
             for (int a = 0; a < 3; ++a) out[a] = m11 * U[a] - m01 * V[a];
         } else { for (int a = 0; a < 3; ++a) out[a] = U[a]; }
     }
@@ -228,42 +241,39 @@ __device__ __forceinline__ void fast_eigen3x3(const double *C, double *out, doub
     if (mc == 0.0) { out[0] = out[1] = out[2] = 0.0; return; }
     double A[6];
 #pragma unroll
-    for (int a = 0; a < 6; ++a) A[a] = C[a] / mc;
+    for (int a = 0; a < 6; ++a) A[a] = o3_div(C[a], mc);
     double norm = (A[1] * A[1] + A[2] * A[2]) + A[4] * A[4];
     if (norm > 0.0) {
-        double q = ((A[0] + A[3]) + A[5]) / 3.0;
+        double q = o3_div((A[0] + A[3]) + A[5], 3.0);
         double b00 = A[0] - q, b11 = A[3] - q, b22 = A[5] - q;
-        double p = sqrt((((b00 * b00 + b11 * b11) + b22 * b22) + norm * 2.0) / 6.0);
+        double p = o3_sqrt(o3_div(((b00 * b00 + b11 * b11) + b22 * b22) + norm * 2.0, 6.0));
         double c00 = b11 * b22 - A[4] * A[4];
         double c01 = A[1] * b22 - A[4] * A[2];
         double c02 = A[1] * A[4] - b11 * A[2];
-        double det = ((b00 * c00 - A[1] * c01) + A[2] * c02) / (p * p * p);
+        double det = o3_div((b00 * c00 - A[1] * c01) + A[2] * c02, p * p * p);
         double half_det = det * 0.5;
         if (half_det < -1.0) half_det = -1.0;
         if (half_det > 1.0) half_det = 1.0;
-        double angle = acos(half_det) / 3.0;
+        double angle = o3_div(acos(half_det), 3.0);
         const double two_thirds_pi = 2.09439510239319549;
         double beta2 = cos(angle) * 2.0;
         double beta0 = cos(angle + two_thirds_pi) * 2.0;
         double beta1 = -(beta0 + beta2);
         double e0 = q + p * beta0, e1 = q + p * beta1, e2 = q + p * beta2;
         if (sep) *sep = p * (beta1 - beta0);      // angle in [0, pi/3]: beta0 <= beta1 <= beta2, so e0 <= e1 <= e2
-        double v0[3], v1[3], v2[3];
-        if (half_det >= 0.0) {
-            eig_vec0(A, e2, v2);
-            if (e2 < e0 && e2 < e1) { out[0] = v2[0]; out[1] = v2[1]; out[2] = v2[2]; return; }
-            eig_vec1(A, v2, e1, v1);
-            if (e1 < e0 && e1 < e2) { out[0] = v1[0]; out[1] = v1[1]; out[2] = v1[2]; return; }
-            cross3d(v1, v2, v0);
-            out[0] = v0[0]; out[1] = v0[1]; out[2] = v0[2];
-        } else {
-            eig_vec0(A, e0, v0);
-            if (e0 < e1 && e0 < e2) { out[0] = v0[0]; out[1] = v0[1]; out[2] = v0[2]; return; }
-            eig_vec1(A, v0, e1, v1);
-            if (e1 < e0 && e1 < e2) { out[0] = v1[0]; out[1] = v1[1]; out[2] = v1[2]; return; }
-            cross3d(v0, v1, v2);
-            out[0] = v2[0]; out[1] = v2[1]; out[2] = v2[2];
-        }
+        // one copy of each solve (the kernels that inline this are instruction-cache bound): the extreme eigenvalue on the
+        // well-conditioned side first (e2 when half_det >= 0, else e0), then e1, the third by the cross product
+        const bool top = half_det >= 0.0;
+        const double ea = top ? e2 : e0, eo = top ? e0 : e2;
+        double va[3], v1[3];
+        eig_vec0(A, ea, va);
+        if (ea < eo && ea < e1) { out[0] = va[0]; out[1] = va[1]; out[2] = va[2]; return; }
+        eig_vec1(A, va, e1, v1);
+        if (e1 < e0 && e1 < e2) { out[0] = v1[0]; out[1] = v1[1]; out[2] = v1[2]; return; }
+        double l[3], r[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { l[a] = top ? v1[a] : va[a]; r[a] = top ? va[a] : v1[a]; }
+        cross3d(l, r, out);
     } else {
         if (sep) {
             const double lo = fmin(A[0], fmin(A[3], A[5])), hi = fmax(A[0], fmax(A[3], A[5]));
@@ -296,7 +306,7 @@ struct Cumul {
         if (n < 3) { C[0] = 1; C[1] = 0; C[2] = 0; C[3] = 1; C[4] = 0; C[5] = 1; return; }
         double m[9], dn = (double)n;
 #pragma unroll
-        for (int a = 0; a < 9; ++a) m[a] = c[a] / dn;
+        for (int a = 0; a < 9; ++a) m[a] = o3_div(c[a], dn);
         C[0] = m[3] - m[0] * m[0];
         C[1] = m[4] - m[0] * m[1];
         C[2] = m[5] - m[0] * m[2];

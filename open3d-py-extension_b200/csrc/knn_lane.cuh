@@ -61,6 +61,13 @@
 #define KL_BND 22       // boundary-bin list entries per query
 #endif
 
+#ifndef KL_BFS
+#define KL_BFS 1        // phase 1 of staging: 1 = level by level (the box loads of a whole level in flight), 0 = depth first
+#endif
+#ifndef KL_BFB
+#define KL_BFB 4        // level-by-level walk: parents whose child boxes are loaded together (6 * KL_BFB loads per lane)
+#endif
+
 #ifndef KL_GUARD
 #define KL_GUARD true   // order-sensitivity guard of the covariance (kf_store_normal); false only for A/B timing
 #endif
@@ -162,6 +169,48 @@ struct KlStage {
         }
     }
 
+    // phase 1, level by level: the frontier (the nodes of one level whose box comes within rho) ping-pongs between the
+    // group list and the histogram area (unused while staging); the child boxes of KL_BFB frontier nodes are loaded
+    // together, so a level costs one memory latency instead of one per visited node.  Children are appended in node
+    // order, which is the depth-first order: the group list is the same.  false = a frontier overflowed (far more
+    // groups than gsplit below it): the attempt is abandoned like one with too many groups.
+    __device__ __forceinline__ bool collect_levels()
+    {
+        const int top = g.levels - 1;
+        const unsigned lt = (1u << lane) - 1u;
+        if (lane == 0) (((top + 1) & 1) ? sm.u.hist : sm.v.gl)[0] = 0u;
+        int ncur = 1;
+        for (int lvl = top; lvl >= 0; --lvl) {
+            __syncwarp();
+            const unsigned *cur = ((lvl + 1) & 1) ? sm.u.hist : sm.v.gl;     // level 0 writes the group list
+            unsigned *nxt = (lvl & 1) ? sm.u.hist : sm.v.gl;
+            const int64_t cnt = g.cnt[lvl];
+            int nout = 0;
+            for (int i = 0; i < ncur; i += KL_BFB) {
+                int64_t c[KL_BFB];
+                float gp[KL_BFB];
+#pragma unroll
+                for (int k = 0; k < KL_BFB; ++k) {
+                    c[k] = i + k < ncur ? (int64_t)cur[i + k] * 32 + lane : cnt;
+                    gp[k] = c[k] < cnt ? gap(lvl, c[k]) : KF_HUGE;
+                }
+#pragma unroll
+                for (int k = 0; k < KL_BFB; ++k) {
+                    const bool take = gp[k] <= rho2f && (lvl > 0 || c[k] != home);
+                    const unsigned m = __ballot_sync(FULL, take);
+                    const int at = nout + __popc(m & lt);
+                    if (take && at < KL_GMAX) nxt[at] = (unsigned)c[k];
+                    nout += __popc(m);
+                }
+                if (nout > (lvl ? KL_GMAX - 32 * KL_BFB : gsplit)) break;
+            }
+            if (lvl && nout > KL_GMAX - 32 * KL_BFB) { ngroups = gsplit + 1; return false; }
+            ncur = nout;
+        }
+        ngroups = ncur;
+        return true;
+    }
+
     __device__ __forceinline__ void append(int64_t p, double x, double y, double z)
     {
         bool in = p < g.n && x >= blo[0] - rho && x <= bhi[0] + rho && y >= blo[1] - rho && y <= bhi[1] + rho &&
@@ -180,6 +229,9 @@ struct KlStage {
 #pragma unroll
         for (int a = 0; a < 3; ++a) { flo[a] = __double2float_rd(blo[a]); fhi[a] = __double2float_ru(bhi[a]); }
         rho2f = __double2float_ru(rho2);
+#if KL_BFS
+        if (!collect_levels()) return false;
+#else
         switch (g.levels - 1) {
         case 0: collect<0>(0); break;
         case 1: collect<1>(0); break;
@@ -188,6 +240,7 @@ struct KlStage {
         case 4: collect<4>(0); break;
         default: collect<5>(0); break;
         }
+#endif
         if (ngroups > gsplit) return false;
         __syncwarp();
         n = 32;
