@@ -169,9 +169,11 @@ __device__ __forceinline__ double dot3d(const double *a, const double *b) { retu
 #if O3_NIDIV
 __device__ __noinline__ double o3_div(double a, double b) { return a / b; }
 __device__ __noinline__ double o3_sqrt(double a) { return sqrt(a); }
+__device__ __noinline__ double o3_cos(double a) { return cos(a); }
 #else
 __device__ __forceinline__ double o3_div(double a, double b) { return a / b; }
 __device__ __forceinline__ double o3_sqrt(double a) { return sqrt(a); }
+__device__ __forceinline__ double o3_cos(double a) { return cos(a); }
 #endif
 
 __device__ __forceinline__ void eig_vec0(const double *A, double ev, double *out)
@@ -256,8 +258,8 @@ __device__ __forceinline__ void fast_eigen3x3(const double *C, double *out, doub
         if (half_det > 1.0) half_det = 1.0;
         double angle = o3_div(acos(half_det), 3.0);
         const double two_thirds_pi = 2.09439510239319549;
-        double beta2 = cos(angle) * 2.0;
-        double beta0 = cos(angle + two_thirds_pi) * 2.0;
+        double beta2 = o3_cos(angle) * 2.0;
+        double beta0 = o3_cos(angle + two_thirds_pi) * 2.0;
         double beta1 = -(beta0 + beta2);
         double e0 = q + p * beta0, e1 = q + p * beta1, e2 = q + p * beta2;
         if (sep) *sep = p * (beta1 - beta0);      // angle in [0, pi/3]: beta0 <= beta1 <= beta2, so e0 <= e1 <= e2

@@ -65,7 +65,8 @@
 #define KL_BFS 1        // phase 1 of staging: 1 = level by level (the box loads of a whole level in flight), 0 = depth first
 #endif
 #ifndef KL_BFB
-#define KL_BFB 4        // level-by-level walk: parents whose child boxes are loaded together (6 * KL_BFB loads per lane)
+#define KL_BFB 1        // level-by-level walk: frontier nodes whose child boxes are loaded together (measured at 10M: 1 -> 10.74 ms,
+                        // 2 -> 10.76, 4 -> 11.37, 8 -> 11.44; depth first 10.96: the kernel is bound by code size, not by these loads)
 #endif
 
 #ifndef KL_GUARD
@@ -186,12 +187,15 @@ struct KlStage {
             unsigned *nxt = (lvl & 1) ? sm.u.hist : sm.v.gl;
             const int64_t cnt = g.cnt[lvl];
             int nout = 0;
-            for (int i = 0; i < ncur; i += KL_BFB) {
+            const int lim = lvl ? KL_GMAX - 32 * KL_BFB : gsplit;
+            int i = 0;
+#if KL_BFB > 1
+            for (; i + KL_BFB <= ncur && nout <= lim; i += KL_BFB) {       // full batches: 6 * KL_BFB box loads in flight
                 int64_t c[KL_BFB];
                 float gp[KL_BFB];
 #pragma unroll
                 for (int k = 0; k < KL_BFB; ++k) {
-                    c[k] = i + k < ncur ? (int64_t)cur[i + k] * 32 + lane : cnt;
+                    c[k] = (int64_t)cur[i + k] * 32 + lane;
                     gp[k] = c[k] < cnt ? gap(lvl, c[k]) : KF_HUGE;
                 }
 #pragma unroll
@@ -202,7 +206,17 @@ struct KlStage {
                     if (take && at < KL_GMAX) nxt[at] = (unsigned)c[k];
                     nout += __popc(m);
                 }
-                if (nout > (lvl ? KL_GMAX - 32 * KL_BFB : gsplit)) break;
+            }
+#endif
+#pragma unroll 1
+            for (; i < ncur && nout <= lim; ++i) {                            // the rest (and the narrow top levels) one by one
+                const int64_t c = (int64_t)cur[i] * 32 + lane;
+                const float gp = c < cnt ? gap(lvl, c) : KF_HUGE;
+                const bool take = gp <= rho2f && (lvl > 0 || c != home);
+                const unsigned m = __ballot_sync(FULL, take);
+                const int at = nout + __popc(m & lt);
+                if (take && at < KL_GMAX) nxt[at] = (unsigned)c;
+                nout += __popc(m);
             }
             if (lvl && nout > KL_GMAX - 32 * KL_BFB) { ngroups = gsplit + 1; return false; }
             ncur = nout;
