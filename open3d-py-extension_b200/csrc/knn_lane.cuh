@@ -25,7 +25,7 @@
 #define KL_WARPS 1
 #endif
 #ifndef KL_CAP
-#define KL_CAP 752      // staged candidates per warp (752 + KL_BND 22 + KL_LIST 56: eleven blocks per SM)
+#define KL_CAP 752      // staged candidates per warp (752 + 2 KL_UNR of padding + KL_BND 22 + KL_LIST 56: eleven blocks per SM)
 #endif
 #ifndef KL_NB
 #define KL_NB 32        // histogram bins
@@ -37,7 +37,8 @@
 #define KL_GSPLIT 192   // more groups than this to scan: split the part without trying
 #endif
 #ifndef KL_UNR
-#define KL_UNR 4       // candidates per iteration of the two select passes
+#define KL_UNR 8       // candidates per iteration of the two select passes (10M, after the code-size cuts: 2 -> 11.52 ms, 4 -> 10.66,
+                       // 8 -> 10.27, 16 -> 10.60)
 #endif
 #ifndef KL_SB
 #define KL_SB 4         // cell groups loaded per staging batch (3 * KL_SB loads in flight per lane)
