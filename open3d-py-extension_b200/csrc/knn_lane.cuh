@@ -66,8 +66,9 @@
 #define KL_BFS 1        // phase 1 of staging: 1 = level by level (the box loads of a whole level in flight), 0 = depth first
 #endif
 #ifndef KL_BFB
-#define KL_BFB 1        // level-by-level walk: frontier nodes whose child boxes are loaded together (measured at 10M: 1 -> 10.74 ms,
-                        // 2 -> 10.76, 4 -> 11.37, 8 -> 11.44; depth first 10.96: the kernel is bound by code size, not by these loads)
+#define KL_BFB 2        // level-by-level walk: frontier nodes whose child boxes are loaded together, unconditionally through a
+                        // clamped index (10M: 1 -> 10.09 ms, 2 -> 9.90, 4 -> 10.15; with a branch around each node's loads 1 -> 10.74,
+                        // 2 -> 10.76, 4 -> 11.37, 8 -> 11.44; depth first 10.96)
 #endif
 
 #ifndef KL_GUARD
@@ -195,10 +196,12 @@ struct KlStage {
                 int64_t c[KL_BFB];
                 float gp[KL_BFB];
 #pragma unroll
-                for (int k = 0; k < KL_BFB; ++k) {
+                for (int k = 0; k < KL_BFB; ++k) {          // unconditional loads (clamped index): all of them in flight together
                     c[k] = (int64_t)cur[i + k] * 32 + lane;
-                    gp[k] = c[k] < cnt ? gap(lvl, c[k]) : KF_HUGE;
+                    gp[k] = gap(lvl, c[k] < cnt ? c[k] : cnt - 1);
                 }
+#pragma unroll
+                for (int k = 0; k < KL_BFB; ++k) if (c[k] >= cnt) gp[k] = KF_HUGE;
 #pragma unroll
                 for (int k = 0; k < KL_BFB; ++k) {
                     const bool take = gp[k] <= rho2f && (lvl > 0 || c[k] != home);
@@ -212,8 +215,8 @@ struct KlStage {
 #pragma unroll 1
             for (; i < ncur && nout <= lim; ++i) {                            // the rest (and the narrow top levels) one by one
                 const int64_t c = (int64_t)cur[i] * 32 + lane;
-                const float gp = c < cnt ? gap(lvl, c) : KF_HUGE;
-                const bool take = gp <= rho2f && (lvl > 0 || c != home);
+                const float gp = gap(lvl, c < cnt ? c : cnt - 1);
+                const bool take = c < cnt && gp <= rho2f && (lvl > 0 || c != home);
                 const unsigned m = __ballot_sync(FULL, take);
                 const int at = nout + __popc(m & lt);
                 if (take && at < KL_GMAX) nxt[at] = (unsigned)c;
@@ -562,11 +565,8 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, int max
                         x[u] = q4.x; y[u] = q4.y; z[u] = q4.z;
                     }
 #pragma unroll
-                    for (int u = 0; u < KL_FPF; ++u) {
-                        if (j0 + u >= A.cn) break;
-                        if (MODE == 2 && !(dist2_rn(px, py, pz, x[u], y[u], z[u]) < r2d)) continue;
-                        cu.add(x[u], y[u], z[u]);
-                    }
+                    for (int u = 0; u < KL_FPF; ++u)
+                        if (j0 + u < A.cn && (MODE != 2 || dist2_rn(px, py, pz, x[u], y[u], z[u]) < r2d)) cu.add(x[u], y[u], z[u]);
                 }
                 answered = kf_store_normal(cu, g.sidx[mypos], out, KL_GUARD);   // false: order-sensitive covariance, exact tier
             }
