@@ -186,7 +186,7 @@ def run_reference(args, rank, world):
     ms = 1e3 * sum(ts) / len(ts)
     val = n / (ms * 1e-3) / 1e6
     sample = f"{n}-point scan from the same generator (seed {SEED_C3}), KNN k={KNN} normals + segment_plane({THR},{RANSAC_N},{ITERS}), OpenMP on all host threads"
-    print(json.dumps({
+    emit(({
         "impl": "reference", "metric": METRIC, "value": val, "unit": "Mpoints/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -195,6 +195,28 @@ def run_reference(args, rank, world):
         "cpu_baseline": {"value": val, "unit": "Mpoints/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "Mpoints/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
+
+
+_JSON_FD = None
+
+
+def claim_stdout():
+    """The driver reads ONE JSON line from stdout, and NCCL prints its version banner there (NCCL_DEBUG=VERSION or
+    higher, set by the box).  Keep the real stdout for the result line and point fd 1 at stderr for everything else."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(line.decode()); sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_JSON_FD, line)
 
 
 def main():
@@ -212,6 +234,7 @@ def main():
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    claim_stdout()
     world = int(os.environ.get("WORLD_SIZE", "1"))
 
     if args.impl == "reference":
@@ -226,8 +249,6 @@ def main():
     torch.cuda.set_device(local)
     dist = None
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"          # NCCL's version banner goes to stdout: keep the JSON line alone there
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
@@ -398,7 +419,7 @@ def main():
                 out["roofline"]["traffic"] = json.load(open(traffic)).get("dram_bytes_per_launch")
             except Exception:
                 pass
-        print(json.dumps(out))
+        emit(out)
     hin.free()
     hout.free()
     ctx.close()
