@@ -54,6 +54,14 @@ enum { O3DPP_SEARCH_KNN = 0, O3DPP_SEARCH_RADIUS = 1, O3DPP_SEARCH_HYBRID = 2 };
 enum { O3DPP_SAMPLER_PHILOX = 0, O3DPP_SAMPLER_MT19937 = 1, O3DPP_SAMPLER_GIVEN = 2 };
 enum { O3DPP_ATTR_POINTS = 0, O3DPP_ATTR_NORMALS = 1, O3DPP_ATTR_COLORS = 2 };
 
+/* o3dpp_set_option: KEEP_NEIGHBORS = every tier of o3dpp_estimate_normals records the neighbour set it selected
+ * (o3dpp_fetch_neighbors); STATS = the search kernels count their work; KNN_* = tuning of the neighbour search
+ * (0 = built-in default; the same knobs are read once per context from the O3DPP_KNN_* environment variables). */
+enum {
+    O3DPP_OPT_KEEP_NEIGHBORS = 1, O3DPP_OPT_STATS = 2, O3DPP_OPT_KNN_RHO = 3, O3DPP_OPT_KNN_GSPLIT = 4,
+    O3DPP_OPT_KNN_MAXSHRINK = 5, O3DPP_OPT_KNN_SHRINK = 6, O3DPP_OPT_KNN_BITS = 7, O3DPP_OPT_KNN_FORCE_LIST = 8
+};
+
 #define O3DPP_MAX_KNN 128
 
 /* ---- library / context ---------------------------------------------------------- */
@@ -70,6 +78,12 @@ O3DPP_API int o3dpp_stream(o3dpp_ctx *ctx, uintptr_t *stream);
  * (PointCloud.py:94-107) and shmIO frames (shmIO.py:229-240). */
 O3DPP_API int o3dpp_host_alloc(void **ptr, uint64_t bytes);
 O3DPP_API int o3dpp_host_free(void *ptr);
+/* Page-lock memory the caller already owns (a named shared-memory frame segment of shmIO.py:39-44, :281-296), so
+ * that uploads from it are direct DMA instead of a staged pageable copy.  Unregister before unmapping it. */
+O3DPP_API int o3dpp_host_register(void *ptr, uint64_t bytes);
+O3DPP_API int o3dpp_host_unregister(void *ptr);
+/* per-context options (O3DPP_OPT_*); the reference has no counterpart: Open3D's search parameters are fixed at build time */
+O3DPP_API int o3dpp_set_option(o3dpp_ctx *ctx, int option, double value);
 /* number of kernels this library has launched on the context since creation */
 O3DPP_API int o3dpp_launch_count(o3dpp_ctx *ctx, uint64_t *count);
 /* ms spent in the last call's stages, measured with CUDA events on the ctx stream.
@@ -86,6 +100,12 @@ O3DPP_API int o3dpp_upload_dev(o3dpp_ctx *ctx, int attr, uintptr_t dev, int64_t 
 /* replaces np.asarray(pcd.points / normals / colors) (PointCloud.py:119-126): float64 (n,3) */
 O3DPP_API int o3dpp_download(o3dpp_ctx *ctx, int attr, double *host);
 O3DPP_API int o3dpp_download_dev(o3dpp_ctx *ctx, int attr, uintptr_t dev, int dtype);
+/* o3dpp_download with the element type of the destination: float32 block mats (PointCloudMat.py:50-51) take
+ * (n,3) float32 straight from the device (PlaneNormalize, processors.py:746-759, returns the mat's dtype) */
+O3DPP_API int o3dpp_download_as(o3dpp_ctx *ctx, int attr, void *host, int dtype);
+/* (n,6) rows [x y z nx ny nz]: np.hstack([pcd[:, :3], normals]) of the CPUNormals block (processors.py:243-249)
+ * assembled on the device and copied once */
+O3DPP_API int o3dpp_download_rows6(o3dpp_ctx *ctx, void *host, int dtype);
 /* as o3dpp_download, but returns at once: the copy runs on a second stream after the work already queued and overlaps
  * the calls that follow (e.g. the normals travel to the host while o3dpp_segment_plane runs; np.asarray(pcd.normals)
  * of PointCloud.py:125 is then free).  `host` (page-locked for a real overlap) is complete, and the attribute may be
@@ -115,6 +135,13 @@ O3DPP_API int o3dpp_transform(o3dpp_ctx *ctx, const double *T16);
  *   seg       V+1 int64 row offsets into `order`
  */
 O3DPP_API int o3dpp_voxel(o3dpp_ctx *ctx, double voxel_size, int64_t *V);
+/* the same with the explicit min_bound / max_bound of the call it replaces (PointCloud.py:339-340): min_bound3 is the
+ * grid origin (Open3D's trace variant does not shift it), max_bound3 only enters the "voxel_size is too small" check;
+ * NULL = the cloud's own bound (o3dpp_voxel).  Points may lie below min_bound3 (negative voxel indices, rows still
+ * ascending).  A scan sharded by spatial slab passes the GLOBAL bounds on every rank, so every rank keys its voxels
+ * exactly as the whole scan would. */
+O3DPP_API int o3dpp_voxel_bounded(o3dpp_ctx *ctx, double voxel_size, const double *min_bound3, const double *max_bound3,
+                                  int64_t *V);
 O3DPP_API int o3dpp_voxel_fetch(o3dpp_ctx *ctx, int32_t *rep_asc, int32_t *rep, int32_t *count,
                                 double *centroid, double *normal, double *color,
                                 int32_t *cubic_id, int32_t *order, int64_t *seg);
@@ -126,8 +153,16 @@ O3DPP_API int o3dpp_voxel_select(o3dpp_ctx *ctx);
  *      fast_normal_computation = True.  mode = O3DPP_SEARCH_*; knn <= O3DPP_MAX_KNN.
  * Normals are written into the context (ATTR_NORMALS); if the cloud already had normals
  * the new ones are flipped to agree with them, as Open3D does.
- * timings: [0] grid build (keys+sort+gather+cell boxes) [1] search+covariance+eigen   */
+ * timings: [0] grid build (keys+sort+gather+cell boxes) [1] search+covariance+eigen; knn <= 32, KNN or hybrid (the
+ * tier chain): [2] tier-1 selection kernel [7] finish kernel (cumulants + eigenvector) [3] compaction + tier 2
+ * [6] compaction + tier 3, [4] / [5] = queries handed to tiers 2 / 3 */
 O3DPP_API int o3dpp_estimate_normals(o3dpp_ctx *ctx, int mode, int knn, double radius);
+/* The neighbour sets behind the last o3dpp_estimate_normals (knn <= 32, KNN or hybrid; O3DPP_OPT_KEEP_NEIGHBORS set before
+ * it): what KDTreeFlann::Search* returned inside pcd.estimate_normals (PointCloud.py:72), as SETS.  queries = m original
+ * point indices (NULL: all n points in order, m ignored).  idx: m*knn int32, each row the ORIGINAL indices of the selected
+ * neighbours in ascending order, -1 padded (hybrid: only those with d2 < radius^2); cnt (nullable): m int32; tier (nullable):
+ * m int8, which kernel of the chain answered the query (1 certified FP32 selection, 2 FP64 range query, 3 exact list search). */
+O3DPP_API int o3dpp_fetch_neighbors(o3dpp_ctx *ctx, const int64_t *queries, int64_t m, int32_t *idx, int32_t *cnt, int8_t *tier);
 /* KDTreeFlann search of every point against the cloud (PointCloud.py:148-163 batched):
  * idx (n*knn int32, -1 padded), d2 (n*knn f64, -1 padded, nullable), cnt (n int32, nullable);
  * rows sorted by (d2, index). Host buffers. */

@@ -49,6 +49,30 @@ interleave_kernel(const double *__restrict__ x, const double *__restrict__ y,
     }
 }
 
+// rows [x y z nx ny nz] (np.hstack([pcd[:, :3], normals]) of the CPUNormals block, reference processors.py:243-249) in one
+// pass: a block moves 128 points, 768 values transposed through shared memory, coalesced both sides
+template <class TOut>
+__global__ void __launch_bounds__(256)
+interleave6_kernel(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
+                   const double *__restrict__ nx, const double *__restrict__ ny, const double *__restrict__ nz,
+                   int64_t n, TOut *__restrict__ rows)
+{
+    __shared__ double sh[768];
+    for (int64_t tile = blockIdx.x; tile * 128 < n; tile += gridDim.x) {
+        int64_t p0 = tile * 128;
+        int64_t cnt = n - p0 < 128 ? n - p0 : 128;
+        const int t = threadIdx.x & 127;
+        if (t < cnt) {
+            if (threadIdx.x < 128) { sh[6 * t] = x[p0 + t]; sh[6 * t + 1] = y[p0 + t]; sh[6 * t + 2] = z[p0 + t]; }
+            else { sh[6 * t + 3] = nx[p0 + t]; sh[6 * t + 4] = ny[p0 + t]; sh[6 * t + 5] = nz[p0 + t]; }
+        }
+        __syncthreads();
+        TOut *dst = rows + p0 * 6;
+        for (int i = threadIdx.x; i < cnt * 6; i += 256) dst[i] = (TOut)sh[i];
+        __syncthreads();
+    }
+}
+
 static Attr3 *attr_of(o3dpp_ctx *c, int attr)
 {
     switch (attr) {
@@ -71,6 +95,7 @@ static void invalidate_derived(o3dpp_ctx *c)
 {
     c->vox_valid = false;
     c->kth_valid = false;
+    c->nbr_valid = false;
     c->r_ninl = -1;
 }
 
@@ -130,6 +155,27 @@ static int download_impl(o3dpp_ctx *c, int attr, void *dst, bool dst_is_device, 
         CU_TRY(cudaMemcpyAsync(dst, ddst, (size_t)n * 3 * esz, cudaMemcpyDeviceToHost, c->stream));
         CU_TRY(cudaStreamSynchronize(c->stream));
     }
+    return 0;
+}
+
+// (n,6) rows [points | normals] to the host in one copy
+static int download_rows6_impl(o3dpp_ctx *c, void *dst, int dtype)
+{
+    if (!c->pts.present || !c->nrm.present) return set_err(O3DPP_E_STATE, "points and normals must be present");
+    if (dtype != O3DPP_F32 && dtype != O3DPP_F64) return set_err(O3DPP_E_ARG, "dtype must be O3DPP_F32 or O3DPP_F64");
+    int64_t n = c->n;
+    if (n == 0) return 0;
+    if (!dst) return set_err(O3DPP_E_ARG, "null destination");
+    size_t esz = dtype == O3DPP_F32 ? 4 : 8;
+    O3_TRY(c->stage.ensure((size_t)n * 6 * esz));
+    int grid = grid_for(c, (n + 127) / 128, 1, 16);
+    if (dtype == O3DPP_F32)
+        LAUNCH(c, interleave6_kernel<float>, grid, 256, 0, c->pts.x(), c->pts.y(), c->pts.z(), c->nrm.x(), c->nrm.y(), c->nrm.z(), n, c->stage.as<float>());
+    else
+        LAUNCH(c, interleave6_kernel<double>, grid, 256, 0, c->pts.x(), c->pts.y(), c->pts.z(), c->nrm.x(), c->nrm.y(), c->nrm.z(), n, c->stage.as<double>());
+    O3_TRY(check_launch("interleave6"));
+    CU_TRY(cudaMemcpyAsync(dst, c->stage.p, (size_t)n * 6 * esz, cudaMemcpyDeviceToHost, c->stream));
+    CU_TRY(cudaStreamSynchronize(c->stream));
     return 0;
 }
 
@@ -258,6 +304,11 @@ __device__ __forceinline__ double row_dot(const double *r, double x, double y, d
                      __dmul_rn(r[3], w));
 }
 
+// point = (T [p,1]).xyz / w.  With an affine T (last row exactly 0 0 0 1) w is 1.0 for every finite point and r / 1.0 == r
+// bit for bit, so the three FP64 divisions (~30 instructions each, the kernel is FP64-issue bound with them) are skipped
+// unless w != 1.0 (a non-finite coordinate makes w NaN: that point takes the division and gets Open3D's NaN).
+__device__ __forceinline__ double persp(double r, double w) { return w == 1.0 ? r : __ddiv_rn(r, w); }
+
 __global__ void __launch_bounds__(256)
 transform_kernel(double *__restrict__ x, double *__restrict__ y, double *__restrict__ z, int64_t n,
                  const __grid_constant__ Mat4 T, int is_normal)
@@ -274,12 +325,12 @@ transform_kernel(double *__restrict__ x, double *__restrict__ y, double *__restr
             oz.x = row_dot(T.m + 8, a.x, b.x, cc.x, 0.0); oz.y = row_dot(T.m + 8, a.y, b.y, cc.y, 0.0);
         } else {
             double w0 = row_dot(T.m + 12, a.x, b.x, cc.x, 1.0), w1 = row_dot(T.m + 12, a.y, b.y, cc.y, 1.0);
-            ox.x = __ddiv_rn(row_dot(T.m + 0, a.x, b.x, cc.x, 1.0), w0);
-            ox.y = __ddiv_rn(row_dot(T.m + 0, a.y, b.y, cc.y, 1.0), w1);
-            oy.x = __ddiv_rn(row_dot(T.m + 4, a.x, b.x, cc.x, 1.0), w0);
-            oy.y = __ddiv_rn(row_dot(T.m + 4, a.y, b.y, cc.y, 1.0), w1);
-            oz.x = __ddiv_rn(row_dot(T.m + 8, a.x, b.x, cc.x, 1.0), w0);
-            oz.y = __ddiv_rn(row_dot(T.m + 8, a.y, b.y, cc.y, 1.0), w1);
+            ox.x = persp(row_dot(T.m + 0, a.x, b.x, cc.x, 1.0), w0);
+            ox.y = persp(row_dot(T.m + 0, a.y, b.y, cc.y, 1.0), w1);
+            oy.x = persp(row_dot(T.m + 4, a.x, b.x, cc.x, 1.0), w0);
+            oy.y = persp(row_dot(T.m + 4, a.y, b.y, cc.y, 1.0), w1);
+            oz.x = persp(row_dot(T.m + 8, a.x, b.x, cc.x, 1.0), w0);
+            oz.y = persp(row_dot(T.m + 8, a.y, b.y, cc.y, 1.0), w1);
         }
         x2[i] = ox; y2[i] = oy; z2[i] = oz;
     }
@@ -292,9 +343,9 @@ transform_kernel(double *__restrict__ x, double *__restrict__ y, double *__restr
             z[i] = row_dot(T.m + 8, a, b, cc, 0.0);
         } else {
             double w = row_dot(T.m + 12, a, b, cc, 1.0);
-            x[i] = __ddiv_rn(row_dot(T.m + 0, a, b, cc, 1.0), w);
-            y[i] = __ddiv_rn(row_dot(T.m + 4, a, b, cc, 1.0), w);
-            z[i] = __ddiv_rn(row_dot(T.m + 8, a, b, cc, 1.0), w);
+            x[i] = persp(row_dot(T.m + 0, a, b, cc, 1.0), w);
+            y[i] = persp(row_dot(T.m + 4, a, b, cc, 1.0), w);
+            z[i] = persp(row_dot(T.m + 8, a, b, cc, 1.0), w);
         }
     }
 }

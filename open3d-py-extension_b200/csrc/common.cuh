@@ -13,6 +13,19 @@
 #include "../../include/o3dpp.h"
 
 #define O3_SM_COUNT_FALLBACK 148
+#define O3_NEV 10
+
+// tuning knobs of the neighbour search (o3dpp_set_option; the O3DPP_KNN_* environment variables are read ONCE, in
+// o3dpp_create, so that sweeps need no rebuild and no call pays a getenv).  0 / negative = the built-in default.
+struct KnnTune {
+    float rho = 0.f;        // staging radius / home-box diagonal
+    int gsplit = 0;         // cell groups to scan beyond which a staging attempt is abandoned
+    int max_shrink = -1;    // shrink retries before a part is given up (12 = never halve)
+    float shrink = 0.f;     // radius factor per retry
+    int bits = 0;           // curve cells per axis = 2^bits
+    bool force_list = false;   // estimate_normals through the FP64 list kernel (A/B timing, parity cross-checks)
+    bool keep = false;      // record the neighbour sets of every tier (o3dpp_fetch_neighbors)
+};
 
 static thread_local std::string g_last_error;
 
@@ -80,10 +93,11 @@ struct o3dpp_ctx {
     cudaStream_t copy_stream = nullptr;   // o3dpp_download_async: device->host copies that overlap the next kernels
     cudaEvent_t copy_ev = nullptr;
     DevBuf stage2;                        // interleaved rows of an asynchronous download
-    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[O3_NEV] = {};
     uint64_t launches = 0;
     double timings[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     bool want_stats = false;              // O3DPP_STATS=1: search kernels count their work
+    KnnTune tune;
     unsigned long long stats[32] = {0};
 
     int64_t n = 0;
@@ -106,6 +120,11 @@ struct o3dpp_ctx {
 
     // KNN grid (Morton-sorted cells, 32-point cell groups and their box hierarchy)
     DevBuf g_sx, g_sy, g_sz, g_sp4, g_sidx, g_box, g_boxf, g_nbr, g_nd2, g_ncnt;
+    DevBuf g_nbrpos, g_tier, g_inv;       // tier chain: neighbour positions [K][pitch], answering tier, original index -> position
+    bool nbr_valid = false;               // g_nbrpos / g_tier hold the sets of the last estimate_normals (keep mode)
+    int nbr_K = 0, nbr_mode = 0;
+    int64_t nbr_pitch = 0;
+    double nbr_radius = 0.0;
 
     // RANSAC
     DevBuf r_samples, r_planes, r_cnt, r_err, r_inl, r_part;

@@ -326,6 +326,13 @@ struct KnnOut {
     double *d2;                 // n*K (nullable)
     int32_t *cnt;               // n (nullable)
     unsigned long long *stats;  // debug counters (nullable): visits, groups loaded, inserts, candidates
+    // tier chain of estimate_normals (knn_lane.cuh): the selected neighbours as sorted positions, [j * nbr_pitch + query
+    // position], KNN_NONE beyond the count.  Tier 1 always writes them (knn_finish_kernel reads them back); with keep != 0
+    // tiers 2 and 3 record theirs too and `tier` says which tier answered (o3dpp_fetch_neighbors)
+    uint32_t *nbr;
+    int64_t nbr_pitch;
+    unsigned char *tier;
+    int keep;
 };
 
 template <int S>
@@ -608,7 +615,7 @@ static int grid_build(o3dpp_ctx *c, GridDesc *gd)
     { int64_t m = 1; int lg = 0; while (m < n) { m <<= 1; ++lg; } bits = (lg + 1) / 2 + 1; }   // ~2 n^(1/2) cells per axis: measured as good as finer grids, one radix pass fewer at 10 M
     if (bits < 8) bits = 8;
     if (bits > 21) bits = 21;
-    if (const char *e = getenv("O3DPP_KNN_BITS")) { int v = atoi(e); if (v >= 4 && v <= 21) bits = v; }   // tuning: curve cells per axis = 2^bits
+    if (c->tune.bits >= 4 && c->tune.bits <= 21) bits = c->tune.bits;   // tuning (O3DPP_OPT_KNN_BITS): curve cells per axis = 2^bits
     size_t nn = (size_t)n + 64;
     O3_TRY(c->s_keys0.ensure(nn * 8)); O3_TRY(c->s_keys1.ensure(nn * 8));
     O3_TRY(c->s_vals0.ensure(nn * 4)); O3_TRY(c->s_vals1.ensure(nn * 4));

@@ -3,21 +3,6 @@
 #include "knn_lane.cuh"
 
 // ---- host side -----------------------------------------------------------------------------------
-template <int MODE>
-static int launch_fast(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, const KnnOut &out)
-{
-    size_t smem = (size_t)KF_WARPS * sizeof(KfWarpMem);
-    auto kern = knn_fast_kernel<MODE>;
-    if (smem > 48 * 1024) CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int64_t blocks = (gd.cnt[0] + KF_WARPS - 1) / KF_WARPS;
-    float rho = 0.5f;
-    if (const char *e = getenv("O3DPP_KNN_RHO")) { float v = (float)atof(e); if (v > 0.f) rho = v; }
-    int dbg = 0;
-    if (const char *e = getenv("O3DPP_KNN_DEBUG_SKIP")) dbg = atoi(e);   // 1: drop failed queries, 2: no tier 2 (timing experiments)
-    LAUNCH(c, kern, (int)blocks, KF_WARPS * 32, smem, gd, K, radius, rho, out, dbg);
-    return check_launch("knn_fast");
-}
-
 struct CapPending {
     const float *cap;
     __device__ __forceinline__ bool operator()(int64_t i) const { return cap[i] >= 0.0f; }
@@ -26,30 +11,48 @@ struct CapPending {
 // tier chain of the lane-per-query path (knn_lane.cuh): tier 1 over every cell group, then the queries it
 // could not certify, compacted in curve order, through the FP64 range query and the exact list search
 template <int MODE>
-static int launch_lane(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, const KnnOut &out)
+static int launch_lane(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, KnnOut out)
 {
     int64_t n = gd.n;
     O3_TRY(c->g_ncnt.ensure((size_t)n * 4 + 64));
     O3_TRY(c->g_nbr.ensure((size_t)n * 4 + 64));
     float *capbuf = c->g_ncnt.as<float>();
     int32_t *list = c->g_nbr.as<int32_t>();
+    // neighbour positions [K][pitch]: tier 1 -> knn_finish_kernel; in keep mode every tier records its sets
+    const int64_t pitch = plane_stride(n);
+    O3_TRY(c->g_nbrpos.ensure((size_t)pitch * K * 4 + 64));
+    out.nbr = c->g_nbrpos.as<uint32_t>();
+    out.nbr_pitch = pitch;
+    out.keep = c->tune.keep ? 1 : 0;
+    out.tier = nullptr;
+    c->nbr_valid = false;
+    if (out.keep) {
+        O3_TRY(c->g_tier.ensure((size_t)n + 64));
+        out.tier = c->g_tier.as<unsigned char>();
+        CU_TRY(cudaMemsetAsync(out.tier, 0, (size_t)n, c->stream));
+    }
     size_t smem = (size_t)KL_WARPS * sizeof(KlWarpMem);
     auto k1 = knn_lane_kernel<MODE>;
     CU_TRY(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int64_t blocks = (gd.cnt[0] + KL_WARPS - 1) / KL_WARPS;
-    float rho = 0.44f;         // staging radius / part-box diagonal (measured optimum on the LiDAR-like scans)
-    if (const char *e = getenv("O3DPP_KNN_RHO")) { float v = (float)atof(e); if (v > 0.f) rho = v; }
-    // a part whose grown box overflows the staging area retries with the radius shrunk (x shrink, up to max_shrink
-    // times), then is halved (never, at the default 12); gsplit = cell groups to scan beyond which an attempt is abandoned before scanning
-    int max_shrink = 12, gsplit = 64;     // gsplit at 10M, all three tiers: 48 -> 13.40 ms, 64 -> 13.23, 80 -> 13.30, 96 -> 13.42, 128 -> 13.47
-    float shrink = 0.7f;
-    if (const char *e = getenv("O3DPP_KNN_MAXSHRINK")) { int v = atoi(e); if (v >= 0 && v <= 12) max_shrink = v; }
-    if (const char *e = getenv("O3DPP_KNN_GSPLIT")) { int v = atoi(e); if (v >= 16 && v <= KL_GMAX - 64) gsplit = v; }
-    if (const char *e = getenv("O3DPP_KNN_SHRINK")) { float v = (float)atof(e); if (v > 0.1f && v < 0.99f) shrink = v; }
+    // rho = staging radius / part-box diagonal (0.44: measured optimum on the LiDAR-like scans).  A part whose grown box
+    // overflows the staging area retries with the radius shrunk (x shrink, up to max_shrink times), then is halved (never,
+    // at the default 12); gsplit = cell groups to scan beyond which an attempt is abandoned before scanning
+    // (10M, all three tiers: 48 -> 13.40 ms, 64 -> 13.23, 80 -> 13.30, 96 -> 13.42, 128 -> 13.47)
+    const KnnTune &t = c->tune;
+    const float rho = t.rho > 0.f ? t.rho : 0.44f;
+    const int max_shrink = t.max_shrink >= 0 && t.max_shrink <= 12 ? t.max_shrink : 12;
+    const int gsplit = t.gsplit >= 16 && t.gsplit <= KL_GMAX - 64 ? t.gsplit : 64;
+    const float shrink = t.shrink > 0.1f && t.shrink < 0.99f ? t.shrink : 0.7f;
     cudaEventRecord(c->ev[3], c->stream);
     LAUNCH(c, k1, (int)blocks, KL_WARPS * 32, smem, gd, K, radius, rho, max_shrink, gsplit, shrink, out, capbuf);
     O3_TRY(check_launch("knn_lane"));
     cudaEventRecord(c->ev[4], c->stream);
+    if (out.nx) {
+        LAUNCH(c, knn_finish_kernel<MODE>, (int)((n + 127) / 128), 128, 0, gd, K, radius, out, capbuf);
+        O3_TRY(check_launch("knn_finish"));
+    }
+    cudaEventRecord(c->ev[6], c->stream);
     int64_t m2 = 0, m3 = 0;
     CapPending pred{capbuf};
     O3_TRY(compact_indices(c, pred, n, list, &m2));
@@ -69,6 +72,7 @@ static int launch_lane(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, c
     c->timings[4] = (double)m2;
     c->timings[5] = (double)m3;
     c->kth_valid = true;
+    if (out.keep) { c->nbr_valid = true; c->nbr_K = K; c->nbr_mode = MODE; c->nbr_pitch = pitch; c->nbr_radius = radius; }
     return 0;
 }
 
@@ -129,11 +133,8 @@ static int search_impl(o3dpp_ctx *c, int mode, int K, double radius, bool want_n
     int rc;
     // estimate_normals with k <= 32 takes the certified FP32 selection kernel; searches that must
     // return sorted (d2, index) lists, k > 32 and pure radius search use the FP64 list kernel
-    static const bool force_list = getenv("O3DPP_KNN_LIST") != nullptr;
-    bool fast = want_normals && !h_idx && K <= 32 && mode != O3DPP_SEARCH_RADIUS && !force_list;
-    static const bool old_fast = getenv("O3DPP_KNN_WARPSELECT") != nullptr;   // previous generation, kept for A/B timing
-    if (fast && !old_fast) rc = mode == 0 ? launch_lane<0>(c, gd, K, radius, out) : launch_lane<2>(c, gd, K, radius, out);
-    else if (fast) rc = mode == 0 ? launch_fast<0>(c, gd, K, radius, out) : launch_fast<2>(c, gd, K, radius, out);
+    const bool fast = want_normals && !h_idx && K <= 32 && mode != O3DPP_SEARCH_RADIUS && !c->tune.force_list;
+    if (fast) rc = mode == 0 ? launch_lane<0>(c, gd, K, radius, out) : launch_lane<2>(c, gd, K, radius, out);
     else if (mode == 0) rc = launch_search_mode<0>(c, gd, K, radius, out);
     else if (mode == 1) rc = launch_search_mode<1>(c, gd, K, radius, out);
     else rc = launch_search_mode<2>(c, gd, K, radius, out);
@@ -150,20 +151,22 @@ static int search_impl(o3dpp_ctx *c, int mode, int K, double radius, bool want_n
     cudaEventElapsedTime(&b, c->ev[1], c->ev[2]);
     c->timings[0] = a;
     c->timings[1] = b;
-    if (fast && !old_fast) {
-        float t1 = 0, t2 = 0;
+    c->timings[2] = c->timings[3] = c->timings[6] = c->timings[7] = 0.0;
+    if (fast) {
+        float t1 = 0, t2 = 0, t3 = 0, tf = 0;
         cudaEventElapsedTime(&t1, c->ev[3], c->ev[4]);
-        float t3 = 0;
-        cudaEventElapsedTime(&t2, c->ev[4], c->ev[5]);
+        cudaEventElapsedTime(&tf, c->ev[4], c->ev[6]);
+        cudaEventElapsedTime(&t2, c->ev[6], c->ev[5]);
         cudaEventElapsedTime(&t3, c->ev[5], c->ev[2]);
-        c->timings[2] = t1;     // tier 1 kernel
+        c->timings[2] = t1;     // tier 1 selection kernel
+        c->timings[7] = tf;     // finish kernel (cumulants + eigenvector of the tier-1 answers)
         c->timings[3] = t2;     // compaction + tier 2
         c->timings[6] = t3;     // compaction + tier 3
         if (c->want_stats && c->stats[16]) {
             double nq = (double)n, nw = (double)c->stats[16];
-            fprintf(stderr, "[o3dpp lane] n=%lld mode=%d K=%d tier1 %.3f ms, tier2 %.3f ms, tier3 %.3f ms (tier2 %lld, tier3 %lld queries) | per warp: parts %.3f candidates %.1f "
+            fprintf(stderr, "[o3dpp lane] n=%lld mode=%d K=%d tier1 %.3f ms, finish %.3f ms, tier2 %.3f ms, tier3 %.3f ms (tier2 %lld, tier3 %lld queries) | per warp: parts %.3f candidates %.1f "
                     "groups-scanned %.1f restages %.3f | fail per query: gap %.4f rho %.4f boundary %.4f count %.4f warp %.4f | split warps %.3f, kcycles per warp: single %.1f split %.1f\n", (long long)n, mode, K,
-                    t1, t2, t3, (long long)c->timings[4], (long long)c->timings[5], c->stats[25] / nw, c->stats[17] / nw, c->stats[18] / nw, c->stats[24] / nw,
+                    t1, tf, t2, t3, (long long)c->timings[4], (long long)c->timings[5], c->stats[25] / nw, c->stats[17] / nw, c->stats[18] / nw, c->stats[24] / nw,
                     c->stats[19] / nq, c->stats[20] / nq, c->stats[21] / nq, c->stats[22] / nq, c->stats[23] / nq,
                     c->stats[28] / nw, c->stats[26] / (nw - c->stats[28] + 1e-9) / 1e3, c->stats[27] / (c->stats[28] + 1e-9) / 1e3);
         }
@@ -198,6 +201,42 @@ static int fetch_kth_impl(o3dpp_ctx *c, float *host)
     LAUNCH(c, kth_scatter_kernel, grid_for(c, n, 256, 16), 256, 0, c->g_ncnt.as<float>(), c->g_sidx.as<uint32_t>(), n, c->g_nd2.as<float>());
     O3_TRY(check_launch("kth_scatter"));
     O3_TRY(d2h(c, host, c->g_nd2.p, (size_t)n * 4));
+    CU_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+
+// o3dpp_fetch_neighbors: the neighbour sets the tier chain of the last estimate_normals selected (keep mode), as ascending
+// original indices.  queries = m original indices (host), nullptr = all points in order.
+static int fetch_neighbors_impl(o3dpp_ctx *c, const int64_t *queries, int64_t m, int32_t *idx, int32_t *cnt, int8_t *tier)
+{
+    if (!c->nbr_valid) return set_err(O3DPP_E_STATE, "no neighbour sets: set O3DPP_OPT_KEEP_NEIGHBORS and run o3dpp_estimate_normals (knn <= 32, KNN or hybrid) first");
+    if (!idx) return set_err(O3DPP_E_ARG, "idx is required");
+    const int64_t n = c->n;
+    if (!queries) m = n;
+    if (m < 0) return set_err(O3DPP_E_ARG, "negative query count");
+    if (m == 0) return 0;
+    const int K = c->nbr_K;
+    GridDesc gd;
+    memset(&gd, 0, sizeof gd);
+    gd.n = n;
+    gd.sp4 = c->g_sp4.as<double4>();
+    gd.sidx = c->g_sidx.as<uint32_t>();
+    O3_TRY(c->g_inv.ensure((size_t)n * 4 + 64));
+    LAUNCH(c, inverse_perm_kernel, grid_for(c, n, 256, 16), 256, 0, gd.sidx, n, c->g_inv.as<uint32_t>());
+    O3_TRY(check_launch("inverse_perm"));
+    // scratch: queries | idx | cnt | tier
+    const size_t oq = 0, oi = oq + (size_t)m * 8, oc = oi + (size_t)m * K * 4, ot = oc + (size_t)m * 4, total = ot + (size_t)m + 64;
+    O3_TRY(c->g_nd2.ensure(total));
+    unsigned char *base = c->g_nd2.as<unsigned char>();
+    if (queries) CU_TRY(cudaMemcpyAsync(base + oq, queries, (size_t)m * 8, cudaMemcpyHostToDevice, c->stream));
+    LAUNCH(c, nbr_fetch_kernel, (int)((m + 127) / 128), 128, 0, gd, c->g_nbrpos.as<uint32_t>(), c->nbr_pitch, c->g_tier.as<unsigned char>(),
+           c->g_inv.as<uint32_t>(), queries ? (const int64_t *)(base + oq) : nullptr, m, K, c->nbr_mode, c->nbr_radius,
+           (int32_t *)(base + oi), (int32_t *)(base + oc), (int8_t *)(base + ot));
+    O3_TRY(check_launch("nbr_fetch"));
+    O3_TRY(d2h(c, idx, base + oi, (size_t)m * K * 4));
+    O3_TRY(d2h(c, cnt, base + oc, (size_t)m * 4));
+    O3_TRY(d2h(c, tier, base + ot, (size_t)m));
     CU_TRY(cudaStreamSynchronize(c->stream));
     return 0;
 }

@@ -14,12 +14,14 @@
 //   CERTIFY  with a = k-th and b = (k+1)-th FP32 d2: the set is the exact FP64 (d2, index) set when
 //     b - a > 2E (E bounds |d2_fp32 - d2_fp64|) and complete when a + E <= rho^2.  Lanes that cannot
 //     certify publish cap = a + E (an upper bound of the true k-th d2) and leave the query to tier 2.
-//   FINISH   FP64 cumulants over the selected neighbours, closed-form eigenvector, store.
+//   OUTPUT   the K selected sorted positions of every certified lane go to global memory ([j][query position], one
+//     coalesced 128-byte store per j); knn_finish_kernel (knn_finish.cuh), a separate full-occupancy launch, turns
+//     them into FP64 cumulants and the closed-form eigenvector.
 // Tier 2 (knn_range_kernel): thread per failed query, exact FP64 range query (d2 <= cap) over the range
 //   tables into a lane-private list, exact (d2, index) selection, finish.  List overflow -> tier 3.
 // Tier 3 (knn_exact_kernel): warp per query, the exact FP64 list search of knn.cuh.
 #pragma once
-#include "knn_fast.cuh"
+#include "knn_finish.cuh"
 
 #ifndef KL_WARPS
 #define KL_WARPS 1
@@ -46,9 +48,6 @@
 #ifndef KL_PIPE
 #define KL_PIPE 0       // select passes: load the next candidates before processing the current ones
 #endif
-#ifndef KL_FPF
-#define KL_FPF 1        // finish: neighbours whose FP64 coordinates are loaded together
-#endif
 #ifndef KL_ATOM
 #define KL_ATOM 1       // histogram update: 1 = shared atomic (fire and forget), 0 = load/add/store
 #endif
@@ -71,9 +70,6 @@
                         // 2 -> 10.76, 4 -> 11.37, 8 -> 11.44; depth first 10.96)
 #endif
 
-#ifndef KL_GUARD
-#define KL_GUARD true   // order-sensitivity guard of the covariance (kf_store_normal); false only for A/B timing
-#endif
 #ifndef KL_LIST
 #define KL_LIST 56      // survivors of the threshold pass per query (16-bit staged slots): < K + KL_BND
 #endif
@@ -549,28 +545,17 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, int max
             A = kl_select<MODE>(sm, lane, np, K, qx, qy, qz, U, tcap, rho1f, eA, eC);
             if (window) { A.ok = false; A.why = 5; }      // rho1f < 0 already refuses; the bound A.capf is what counts
         } else if (nq >= K) A.capf = U + kf_err(U, eA, eC) * 1.0001f;
+        if (out.stats && inpart && valid) { n1 += A.why == 1; n2 += A.why == 2; n3 += A.why == 3; n4 += A.why == 4; n5 += A.why == 5; }
+        // OUTPUT: sorted positions of the selected neighbours, [j][query position]; KNN_NONE beyond the count
+        const bool put = inpart && valid && A.ok && out.nbr != nullptr;
+        if (__any_sync(FULL, put)) {
+            uint32_t *dst = out.nbr + mypos;
+            for (int j = 0; j < K; ++j)
+                if (put) dst[(int64_t)j * out.nbr_pitch] = j < A.cn ? (uint32_t)kl_pos(sm.cand, sm.v.nb[j * 32 + lane]) : KNN_NONE;
+        }
         if (inpart && valid) {
-            bool answered = A.ok;
-            if (out.stats) { n1 += A.why == 1; n2 += A.why == 2; n3 += A.why == 3; n4 += A.why == 4; n5 += A.why == 5; }
-            if (A.ok && out.nx) {
-                Cumul cu;
-                cu.clear();
-                for (int j0 = 0; j0 < A.cn; j0 += KL_FPF) {        // KL_FPF neighbours' coordinates in flight
-                    double x[KL_FPF], y[KL_FPF], z[KL_FPF];
-#pragma unroll
-                    for (int u = 0; u < KL_FPF; ++u) {
-                        int j = j0 + u < A.cn ? j0 + u : A.cn - 1;
-                        int p = kl_pos(sm.cand, sm.v.nb[j * 32 + lane]);
-                        const double4 q4 = g.sp4[p];
-                        x[u] = q4.x; y[u] = q4.y; z[u] = q4.z;
-                    }
-#pragma unroll
-                    for (int u = 0; u < KL_FPF; ++u)
-                        if (j0 + u < A.cn && (MODE != 2 || dist2_rn(px, py, pz, x[u], y[u], z[u]) < r2d)) cu.add(x[u], y[u], z[u]);
-                }
-                answered = kf_store_normal(cu, g.sidx[mypos], out, KL_GUARD);   // false: order-sensitive covariance, exact tier
-            }
-            capbuf[mypos] = answered ? -fmaxf(A.capf, 1e-30f) : A.capf;   // negative = answered, magnitude bounds the k-th d2
+            capbuf[mypos] = A.ok ? -fmaxf(A.capf, 1e-30f) : A.capf;   // negative = answered, magnitude bounds the k-th d2
+            if (out.keep && A.ok) out.tier[mypos] = 1;
         }
         __syncwarp();
         start += len;
@@ -615,6 +600,7 @@ knn_lane_kernel(const GridDesc g, int K, double radius, float rho_scale, int max
 struct K2WarpMem {
     double d[K2_LIST], x[K2_LIST], y[K2_LIST], z[K2_LIST];
     unsigned oidx[K2_LIST];
+    unsigned pos[K2_LIST];      // sorted position (neighbour-set record, keep mode)
 };
 
 // lower bound (FP32, every step rounded down, boxes stored rounded outwards) of the squared distance from q to box c
@@ -650,7 +636,7 @@ struct K2Range {
         }
         unsigned m = __ballot_sync(FULL, hit);
         int at = cnt + __popc(m & ((1u << lane) - 1u));
-        if (hit && at < K2_LIST) { sm.d[at] = d; sm.x[at] = x; sm.y[at] = y; sm.z[at] = z; sm.oidx[at] = g.sidx[p]; }
+        if (hit && at < K2_LIST) { sm.d[at] = d; sm.x[at] = x; sm.y[at] = y; sm.z[at] = z; sm.oidx[at] = g.sidx[p]; sm.pos[at] = (unsigned)p; }
         cnt += __popc(m);
         if (K2_SHRINK && cnt > K2_LIST - 32) shrink();
     }
@@ -661,13 +647,13 @@ struct K2Range {
         __syncwarp();
         constexpr int PER = K2_LIST / 32;
         double de[PER], xe[PER], ye[PER], ze[PER];
-        unsigned oe[PER];
+        unsigned oe[PER], pe[PER];
         int rank[PER];
 #pragma unroll
         for (int a = 0; a < PER; ++a) {
             int e = a * 32 + lane;
             bool ve = e < cnt;
-            de[a] = ve ? sm.d[e] : pos_inf(); oe[a] = ve ? sm.oidx[e] : 0xffffffffu;
+            de[a] = ve ? sm.d[e] : pos_inf(); oe[a] = ve ? sm.oidx[e] : 0xffffffffu; pe[a] = ve ? sm.pos[e] : 0u;
             xe[a] = ve ? sm.x[e] : 0.0; ye[a] = ve ? sm.y[e] : 0.0; ze[a] = ve ? sm.z[e] : 0.0;
             rank[a] = 0;
         }
@@ -682,7 +668,7 @@ struct K2Range {
 #pragma unroll
         for (int a = 0; a < PER; ++a) {
             bool keep = a * 32 + lane < cnt && rank[a] < K;      // ranks are distinct: exactly K survive
-            if (keep) { int r = rank[a]; sm.d[r] = de[a]; sm.x[r] = xe[a]; sm.y[r] = ye[a]; sm.z[r] = ze[a]; sm.oidx[r] = oe[a]; }
+            if (keep) { int r = rank[a]; sm.d[r] = de[a]; sm.x[r] = xe[a]; sm.y[r] = ye[a]; sm.z[r] = ze[a]; sm.oidx[r] = oe[a]; sm.pos[r] = pe[a]; }
             if (keep && rank[a] == K - 1) kth = de[a];
         }
 #pragma unroll
@@ -779,6 +765,7 @@ knn_range_kernel(const GridDesc g, int K, double radius, KnnOut out, const int32
         const int cnt = rq.cnt;
         if (cnt > K2_LIST) continue;             // (K2_SHRINK == 0) too many candidates inside the bound: tier 3
         __syncwarp();
+        const int64_t qpos = __shfl_sync(FULL, myq, i);
         // rank by (d2, original index); the K smallest contribute
         Cumul cu;
         cu.clear();
@@ -795,7 +782,14 @@ knn_range_kernel(const GridDesc g, int K, double radius, KnnOut out, const int32
                     unsigned of = sm.oidx[f];
                     rank += (df < de || (df == de && of < oe)) ? 1 : 0;
                 }
-            if (ve && rank < K) { cu.add(sm.x[e], sm.y[e], sm.z[e]); kd = fmax(kd, de); }
+            if (ve && rank < K) {
+                cu.add(sm.x[e], sm.y[e], sm.z[e]); kd = fmax(kd, de);
+                if (out.keep) out.nbr[(int64_t)(cnt > K ? rank : e) * out.nbr_pitch + qpos] = sm.pos[e];     // ranks are distinct
+            }
+        }
+        if (out.keep) {
+            for (int j = (cnt < K ? cnt : K) + lane; j < K; j += 32) out.nbr[(int64_t)j * out.nbr_pitch + qpos] = KNN_NONE;
+            if (lane == 0) out.tier[qpos] = 2;
         }
 #pragma unroll
         for (int dlt = 16; dlt > 0; dlt >>= 1) kd = fmax(kd, shfl_xor_d(kd, dlt));

@@ -40,11 +40,18 @@ O3DPP_API int o3dpp_create(int device, o3dpp_ctx **out)
     CU_TRY(cudaGetDeviceProperties(&prop, device));
     c->sm_count = prop.multiProcessorCount > 0 ? prop.multiProcessorCount : O3_SM_COUNT_FALLBACK;
     CU_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    for (int i = 0; i < 6; ++i) CU_TRY(cudaEventCreate(&c->ev[i]));
+    for (int i = 0; i < O3_NEV; ++i) CU_TRY(cudaEventCreate(&c->ev[i]));
     CU_TRY(cudaHostAlloc(&c->h_small, 64 * 1024, cudaHostAllocDefault));
     O3_TRY(c->d_small.ensure(64 * 1024));
+    // tuning defaults from the environment, read once per context (sweeps without a rebuild); o3dpp_set_option overrides
     const char *e = getenv("O3DPP_STATS");
     c->want_stats = e && e[0] == '1';
+    if ((e = getenv("O3DPP_KNN_RHO"))) c->tune.rho = (float)atof(e);
+    if ((e = getenv("O3DPP_KNN_GSPLIT"))) c->tune.gsplit = atoi(e);
+    if ((e = getenv("O3DPP_KNN_MAXSHRINK"))) c->tune.max_shrink = atoi(e);
+    if ((e = getenv("O3DPP_KNN_SHRINK"))) c->tune.shrink = (float)atof(e);
+    if ((e = getenv("O3DPP_KNN_BITS"))) c->tune.bits = atoi(e);
+    if (getenv("O3DPP_KNN_LIST")) c->tune.force_list = true;
     *out = c;
     return 0;
 }
@@ -60,10 +67,10 @@ O3DPP_API int o3dpp_destroy(o3dpp_ctx *c)
                       &c->s_vals0, &c->s_vals1, &c->s_hist, &c->s_scan, &c->s_scan2, &c->s_flags, &c->v_order,
                       &c->v_seg, &c->v_oct, &c->v_rep, &c->v_rep_asc, &c->v_count, &c->v_centroid, &c->v_normal,
                       &c->v_color, &c->v_cubic, &c->g_sx, &c->g_sy, &c->g_sz, &c->g_sidx, &c->g_box, &c->g_nbr,
-                      &c->g_nd2, &c->g_ncnt, &c->g_sp4, &c->g_boxf, &c->r_samples, &c->r_planes, &c->r_cnt, &c->r_err, &c->r_inl, &c->r_part};
+                      &c->g_nd2, &c->g_ncnt, &c->g_sp4, &c->g_boxf, &c->g_nbrpos, &c->g_tier, &c->g_inv, &c->r_samples, &c->r_planes, &c->r_cnt, &c->r_err, &c->r_inl, &c->r_part};
     for (DevBuf *b : bufs) b->release();
     if (c->h_small) cudaFreeHost(c->h_small);
-    for (int i = 0; i < 6; ++i) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    for (int i = 0; i < O3_NEV; ++i) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return 0;
@@ -95,6 +102,36 @@ O3DPP_API int o3dpp_host_alloc(void **ptr, uint64_t bytes)
 O3DPP_API int o3dpp_host_free(void *ptr)
 {
     if (ptr) CU_TRY(cudaFreeHost(ptr));
+    return 0;
+}
+
+O3DPP_API int o3dpp_host_register(void *ptr, uint64_t bytes)
+{
+    if (!ptr || !bytes) return set_err(O3DPP_E_ARG, "null range");
+    CU_TRY(cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+    return 0;
+}
+
+O3DPP_API int o3dpp_host_unregister(void *ptr)
+{
+    if (ptr) CU_TRY(cudaHostUnregister(ptr));
+    return 0;
+}
+
+O3DPP_API int o3dpp_set_option(o3dpp_ctx *c, int option, double value)
+{
+    if (!c) return set_err(O3DPP_E_ARG, "null context");
+    switch (option) {
+    case O3DPP_OPT_KEEP_NEIGHBORS: c->tune.keep = value != 0.0; if (!c->tune.keep) c->nbr_valid = false; break;
+    case O3DPP_OPT_STATS: c->want_stats = value != 0.0; break;
+    case O3DPP_OPT_KNN_RHO: c->tune.rho = (float)value; break;
+    case O3DPP_OPT_KNN_GSPLIT: c->tune.gsplit = (int)value; break;
+    case O3DPP_OPT_KNN_MAXSHRINK: c->tune.max_shrink = (int)value; break;
+    case O3DPP_OPT_KNN_SHRINK: c->tune.shrink = (float)value; break;
+    case O3DPP_OPT_KNN_BITS: c->tune.bits = (int)value; break;
+    case O3DPP_OPT_KNN_FORCE_LIST: c->tune.force_list = value != 0.0; break;
+    default: return set_err(O3DPP_E_ARG, "unknown option");
+    }
     return 0;
 }
 
@@ -142,6 +179,19 @@ O3DPP_API int o3dpp_download(o3dpp_ctx *c, int attr, double *host)
     return download_impl(c, attr, host, false, O3DPP_F64);
 }
 
+O3DPP_API int o3dpp_download_as(o3dpp_ctx *c, int attr, void *host, int dtype)
+{
+    CTX_CHECK(c);
+    if (dtype != O3DPP_F32 && dtype != O3DPP_F64) return set_err(O3DPP_E_ARG, "dtype must be O3DPP_F32 or O3DPP_F64");
+    return download_impl(c, attr, host, false, dtype);
+}
+
+O3DPP_API int o3dpp_download_rows6(o3dpp_ctx *c, void *host, int dtype)
+{
+    CTX_CHECK(c);
+    return download_rows6_impl(c, host, dtype);
+}
+
 O3DPP_API int o3dpp_download_async(o3dpp_ctx *c, int attr, double *host)
 {
     CTX_CHECK(c);
@@ -151,6 +201,7 @@ O3DPP_API int o3dpp_download_async(o3dpp_ctx *c, int attr, double *host)
 O3DPP_API int o3dpp_download_dev(o3dpp_ctx *c, int attr, uintptr_t dev, int dtype)
 {
     CTX_CHECK(c);
+    if (dtype != O3DPP_F32 && dtype != O3DPP_F64) return set_err(O3DPP_E_ARG, "dtype must be O3DPP_F32 or O3DPP_F64");
     O3_TRY(download_impl(c, attr, (void *)dev, true, dtype));
     CU_TRY(cudaStreamSynchronize(c->stream));
     return 0;
@@ -208,7 +259,13 @@ O3DPP_API int o3dpp_transform(o3dpp_ctx *c, const double *T16)
 O3DPP_API int o3dpp_voxel(o3dpp_ctx *c, double voxel_size, int64_t *V)
 {
     CTX_CHECK(c);
-    return voxel_impl(c, voxel_size, V);
+    return voxel_impl(c, voxel_size, nullptr, nullptr, V);
+}
+
+O3DPP_API int o3dpp_voxel_bounded(o3dpp_ctx *c, double voxel_size, const double *min_bound3, const double *max_bound3, int64_t *V)
+{
+    CTX_CHECK(c);
+    return voxel_impl(c, voxel_size, min_bound3, max_bound3, V);
 }
 
 O3DPP_API int o3dpp_voxel_fetch(o3dpp_ctx *c, int32_t *rep_asc, int32_t *rep, int32_t *count, double *centroid,
@@ -251,6 +308,7 @@ O3DPP_API int o3dpp_fetch_inliers(o3dpp_ctx *c, int32_t *out)
 {
     CTX_CHECK(c);
     if (c->r_ninl < 0) return set_err(O3DPP_E_STATE, "o3dpp_segment_plane has not been run on the current cloud");
+    if (!out && c->r_ninl > 0) return set_err(O3DPP_E_ARG, "null output buffer");
     O3_TRY(d2h(c, out, c->r_inl.p, (size_t)c->r_ninl * 4));
     CU_TRY(cudaStreamSynchronize(c->stream));
     return 0;
@@ -329,6 +387,11 @@ O3DPP_API int o3dpp_inlier_moments(o3dpp_ctx *c, const double *centroid3, double
     CTX_CHECK(c);
     if (!centroid3 || !mom6) return set_err(O3DPP_E_ARG, "null argument");
     return inlier_moments_impl(c, centroid3, mom6);
+}
+O3DPP_API int o3dpp_fetch_neighbors(o3dpp_ctx *c, const int64_t *queries, int64_t m, int32_t *idx, int32_t *cnt, int8_t *tier)
+{
+    CTX_CHECK(c);
+    return fetch_neighbors_impl(c, queries, m, idx, cnt, tier);
 }
 O3DPP_API int o3dpp_fetch_kth_bound(o3dpp_ctx *c, float *out)
 {

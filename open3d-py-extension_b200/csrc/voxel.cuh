@@ -10,13 +10,17 @@
 #include "cloud.cuh"
 
 struct VoxPack { int bx, by, bz; };  // bits per axis in the packed key
+struct VoxOrigin {                   // grid origin (min_bound) and the smallest voxel index per axis: keys are index - lo >= 0
+    double o[3];
+    int64_t lo[3];
+};
 
 __global__ void __launch_bounds__(256)
 voxel_key_kernel(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
-                 int64_t n, const double *__restrict__ mn, double voxel_size, VoxPack pk, int wide,
+                 int64_t n, const VoxOrigin og, double voxel_size, VoxPack pk, int wide,
                  uint64_t *__restrict__ key_lo, uint32_t *__restrict__ key_ix, uint8_t *__restrict__ oct)
 {
-    double m0 = mn[0], m1 = mn[1], m2 = mn[2];
+    const double m0 = og.o[0], m1 = og.o[1], m2 = og.o[2];
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         double r0 = __ddiv_rn(__dsub_rn(x[i], m0), voxel_size);
         double r1 = __ddiv_rn(__dsub_rn(y[i], m1), voxel_size);
@@ -27,7 +31,8 @@ voxel_key_kernel(const double *__restrict__ x, const double *__restrict__ y, con
         if (__dsub_rn(r1, f1) >= 0.5) o |= 2;
         if (__dsub_rn(r2, f2) >= 0.5) o |= 4;
         oct[i] = (uint8_t)o;
-        uint64_t ix = (uint64_t)(uint32_t)(int32_t)f0, iy = (uint64_t)(uint32_t)(int32_t)f1, iz = (uint64_t)(uint32_t)(int32_t)f2;
+        // voxel index relative to the smallest index of the cloud: non-negative, row order unchanged
+        uint64_t ix = (uint64_t)((int64_t)f0 - og.lo[0]), iy = (uint64_t)((int64_t)f1 - og.lo[1]), iz = (uint64_t)((int64_t)f2 - og.lo[2]);
         if (wide) {
             key_lo[i] = (iy << pk.bz) | iz;
             key_ix[i] = (uint32_t)ix;
@@ -118,7 +123,10 @@ static int bit_length_u32(uint32_t v)
     return b < 1 ? 1 : b;
 }
 
-static int voxel_impl(o3dpp_ctx *c, double voxel_size, int64_t *Vout)
+// min3 / max3 (nullable): the explicit min_bound / max_bound of the call being replaced (PointCloud.py:339-340); Open3D's
+// trace variant takes min_bound itself as the grid origin and uses max_bound only in the size check.  nullptr = the
+// cloud's own bounds (what the reference passes).  A slab-sharded scan passes the GLOBAL bounds on every rank.
+static int voxel_impl(o3dpp_ctx *c, double voxel_size, const double *min3, const double *max3, int64_t *Vout)
 {
     if (Vout) *Vout = 0;
     if (!(voxel_size > 0.0)) return set_err(O3DPP_E_VOXEL_SIZE, "voxel_size <= 0.");
@@ -127,15 +135,29 @@ static int voxel_impl(o3dpp_ctx *c, double voxel_size, int64_t *Vout)
     double mn[3], mx[3];
     cudaEventRecord(c->ev[0], c->stream);
     O3_TRY(bounds_impl(c, mn, mx));
-    double ext = mx[0] - mn[0];
-    if (mx[1] - mn[1] > ext) ext = mx[1] - mn[1];
-    if (mx[2] - mn[2] > ext) ext = mx[2] - mn[2];
+    VoxOrigin og;
+    double far3[3];
+    for (int a = 0; a < 3; ++a) {
+        og.o[a] = min3 ? min3[a] : mn[a];
+        far3[a] = max3 ? max3[a] : mx[a];
+        if (!(og.o[a] == og.o[a]) || !(far3[a] == far3[a])) return set_err(O3DPP_E_ARG, "min_bound / max_bound must not be NaN");
+    }
+    double ext = far3[0] - og.o[0];
+    if (far3[1] - og.o[1] > ext) ext = far3[1] - og.o[1];
+    if (far3[2] - og.o[2] > ext) ext = far3[2] - og.o[2];
     if (voxel_size * 2147483647.0 < ext) return set_err(O3DPP_E_VOXEL_SMALL, "voxel_size is too small.");
     if (n == 0) { c->vox_valid = true; c->vox_V = 0; c->vox_n = 0; return 0; }
-    // the largest index per axis comes from the max bound through the very same expression
+    // the smallest / largest index per axis come from the cloud's own bounds through the very same expression
+    // (subtraction and division by a positive number are monotone under rounding)
     VoxPack pk;
     uint32_t mi[3];
-    for (int a = 0; a < 3; ++a) mi[a] = (uint32_t)(int32_t)floor((mx[a] - mn[a]) / voxel_size);
+    for (int a = 0; a < 3; ++a) {
+        const double flo = floor((mn[a] - og.o[a]) / voxel_size), fhi = floor((mx[a] - og.o[a]) / voxel_size);
+        if (!(flo >= -2147483648.0) || !(fhi <= 2147483647.0))      // points outside the given bounds: Open3D's int cast would overflow
+            return set_err(O3DPP_E_VOXEL_SMALL, "voxel_size is too small.");
+        og.lo[a] = (int64_t)flo;
+        mi[a] = (uint32_t)((int64_t)fhi - og.lo[a]);
+    }
     pk.bx = bit_length_u32(mi[0]); pk.by = bit_length_u32(mi[1]); pk.bz = bit_length_u32(mi[2]);
     int wide = (pk.bx + pk.by + pk.bz) > 64;
 
@@ -152,7 +174,7 @@ static int voxel_impl(o3dpp_ctx *c, double voxel_size, int64_t *Vout)
         key_ix = wide_ix.as<uint32_t>();
     }
     int grid = grid_for(c, n, 256, 16);
-    LAUNCH(c, voxel_key_kernel, grid, 256, 0, c->pts.x(), c->pts.y(), c->pts.z(), n, c->d_small.as<double>(),
+    LAUNCH(c, voxel_key_kernel, grid, 256, 0, c->pts.x(), c->pts.y(), c->pts.z(), n, og,
            voxel_size, pk, wide, key_lo, key_ix, c->v_oct.as<uint8_t>());
     O3_TRY(check_launch("voxel_key"));
     uint64_t *ks = nullptr;

@@ -19,6 +19,8 @@ SEARCH_KNN, SEARCH_RADIUS, SEARCH_HYBRID = 0, 1, 2
 SAMPLER_PHILOX, SAMPLER_MT19937, SAMPLER_GIVEN = 0, 1, 2
 F32, F64 = 0, 1
 MAX_KNN = 128
+(OPT_KEEP_NEIGHBORS, OPT_STATS, OPT_KNN_RHO, OPT_KNN_GSPLIT, OPT_KNN_MAXSHRINK, OPT_KNN_SHRINK, OPT_KNN_BITS,
+ OPT_KNN_FORCE_LIST) = range(1, 9)
 
 # every symbol include/o3dpp.h declares (tests check the library exports all of them)
 SYMBOLS = [
@@ -30,6 +32,8 @@ SYMBOLS = [
     "o3dpp_segment_plane", "o3dpp_fetch_inliers", "o3dpp_fetch_samples", "o3dpp_select",
     "o3dpp_select_inliers", "o3dpp_sample_philox", "o3dpp_planes_from_points", "o3dpp_score_planes",
     "o3dpp_plane_inliers", "o3dpp_inlier_moments", "o3dpp_fetch_kth_bound", "o3dpp_knn_mean_distance", "o3dpp_zsplat", "o3dpp_download_async",
+    "o3dpp_set_option", "o3dpp_fetch_neighbors", "o3dpp_voxel_bounded", "o3dpp_download_as", "o3dpp_download_rows6",
+    "o3dpp_host_register", "o3dpp_host_unregister",
 ]
 
 _lib = None
@@ -106,13 +110,26 @@ class PinnedArray:
         self.free()
 
 
+def host_register(arr):
+    """page-lock the memory behind a numpy array the caller owns (e.g. a shared-memory frame segment)"""
+    _check(lib().o3dpp_host_register(C.c_void_p(arr.ctypes.data), C.c_uint64(arr.nbytes)))
+
+
+def host_unregister(arr):
+    _check(lib().o3dpp_host_unregister(C.c_void_p(arr.ctypes.data)))
+
+
 class Context:
-    """One device-resident cloud on one GPU (o3dpp_ctx).  Created lazily, per process."""
+    """One device-resident cloud on one GPU (o3dpp_ctx).  Created lazily, per process.
+
+    `generation` counts the changes of the device points (upload, transform, selection): the pipeline blocks use it
+    to tell whether the cloud they left on the device is still the one they find (processors._DeviceBlock)."""
 
     def __init__(self, device=0):
         self._h = C.c_void_p()
         self.device = device
         self._pid = os.getpid()
+        self.generation = 0
         _check(lib().o3dpp_create(C.c_int(device), C.byref(self._h)))
 
     def close(self):
@@ -138,10 +155,30 @@ class Context:
         if a.ndim != 2 or a.shape[1] != 3:
             raise ValueError("expected an (n,3) array")
         a = np.ascontiguousarray(a)
+        if attr == ATTR_POINTS:
+            self.generation += 1
         _check(lib().o3dpp_upload(self._h, C.c_int(attr), _ptr(a), C.c_int64(a.shape[0]), C.c_int(dt)))
 
     def upload_dev(self, attr, dev_ptr, n, dtype=F64):
+        if attr == ATTR_POINTS:
+            self.generation += 1
         _check(lib().o3dpp_upload_dev(self._h, C.c_int(attr), C.c_size_t(dev_ptr), C.c_int64(n), C.c_int(dtype)))
+
+    def download_as(self, attr, out):
+        """(n,3) float32 or float64 C-contiguous destination"""
+        n = self.size()
+        assert out.dtype in (np.float32, np.float64) and out.flags.c_contiguous and out.shape == (n, 3)
+        if n:
+            _check(lib().o3dpp_download_as(self._h, C.c_int(attr), _ptr(out), C.c_int(F32 if out.dtype == np.float32 else F64)))
+        return out
+
+    def download_rows6(self, out):
+        """(n,6) rows [x y z nx ny nz], float32 or float64"""
+        n = self.size()
+        assert out.dtype in (np.float32, np.float64) and out.flags.c_contiguous and out.shape == (n, 6)
+        if n:
+            _check(lib().o3dpp_download_rows6(self._h, _ptr(out), C.c_int(F32 if out.dtype == np.float32 else F64)))
+        return out
 
     def download(self, attr, out=None):
         n = self.size()
@@ -174,6 +211,8 @@ class Context:
         return bool(f.value)
 
     def drop(self, attr):
+        if attr == ATTR_POINTS:
+            self.generation += 1
         _check(lib().o3dpp_drop(self._h, C.c_int(attr)))
 
     def synchronize(self):
@@ -207,11 +246,18 @@ class Context:
     # ---- operations
     def transform(self, T):
         T = np.ascontiguousarray(np.asarray(T, dtype=np.float64).reshape(16))
+        self.generation += 1
         _check(lib().o3dpp_transform(self._h, _ptr(T)))
 
-    def voxel(self, voxel_size):
+    def voxel(self, voxel_size, min_bound=None, max_bound=None):
+        """min_bound / max_bound: explicit grid origin / far corner (None: the cloud's own bounds)"""
         V = C.c_int64(0)
-        _check(lib().o3dpp_voxel(self._h, C.c_double(voxel_size), C.byref(V)))
+        if min_bound is None and max_bound is None:
+            _check(lib().o3dpp_voxel(self._h, C.c_double(voxel_size), C.byref(V)))
+        else:
+            mn = None if min_bound is None else np.ascontiguousarray(np.asarray(min_bound, dtype=np.float64).reshape(3))
+            mx = None if max_bound is None else np.ascontiguousarray(np.asarray(max_bound, dtype=np.float64).reshape(3))
+            _check(lib().o3dpp_voxel_bounded(self._h, C.c_double(voxel_size), _ptr(mn), _ptr(mx), C.byref(V)))
         return V.value
 
     def voxel_fetch(self, V, n, fields=("rep_asc",)):
@@ -227,10 +273,29 @@ class Context:
         return out
 
     def voxel_select(self):
+        self.generation += 1
         _check(lib().o3dpp_voxel_select(self._h))
 
     def estimate_normals(self, mode, knn, radius):
         _check(lib().o3dpp_estimate_normals(self._h, C.c_int(mode), C.c_int(knn), C.c_double(radius)))
+
+    def set_option(self, option, value):
+        _check(lib().o3dpp_set_option(self._h, C.c_int(option), C.c_double(float(value))))
+
+    def fetch_neighbors(self, knn, queries=None):
+        """neighbour sets of the last estimate_normals (OPT_KEEP_NEIGHBORS set before it): (idx (m,knn) int32 ascending
+        original indices, -1 padded; cnt (m,) int32; tier (m,) int8 = which kernel of the chain answered)"""
+        if queries is None:
+            m, q = self.size(), None
+        else:
+            q = np.ascontiguousarray(np.asarray(queries, dtype=np.int64).reshape(-1))
+            m = q.size
+        idx = np.empty((m, knn), np.int32)
+        cnt = np.empty(m, np.int32)
+        tier = np.empty(m, np.int8)
+        if m:
+            _check(lib().o3dpp_fetch_neighbors(self._h, _ptr(q), C.c_int64(m), _ptr(idx), _ptr(cnt), _ptr(tier)))
+        return idx, cnt, tier
 
     def knn(self, mode, knn, radius=0.0, want_d2=True):
         n = self.size()
@@ -283,9 +348,11 @@ class Context:
 
     def select(self, idx, invert=False):
         idx = np.ascontiguousarray(np.asarray(idx, dtype=np.int32).reshape(-1))
+        self.generation += 1
         _check(lib().o3dpp_select(self._h, _ptr(idx), C.c_int64(idx.size), C.c_int(int(invert))))
 
     def select_inliers(self, invert=False):
+        self.generation += 1
         _check(lib().o3dpp_select_inliers(self._h, C.c_int(int(invert))))
 
     # ---- the steps of segment_plane for slab-sharded scans (sharding.py)
@@ -356,6 +423,17 @@ class Context:
 
 
 _contexts = {}
+_ctx_locks = {}
+
+
+def context_lock(device=0):
+    """re-entrant lock that serialises the calls of one process on the shared context of a device"""
+    key = (os.getpid(), int(device))
+    lk = _ctx_locks.get(key)
+    if lk is None:
+        with _lock:
+            lk = _ctx_locks.setdefault(key, threading.RLock())
+    return lk
 
 
 def context(device=0):

@@ -10,6 +10,7 @@ CUDA kernels and writes the results back.  Inside `with cloud.resident():` the c
 the GPU between calls and host arrays are refreshed only when they are read.
 """
 import contextlib
+import functools
 import os
 
 import numpy as np
@@ -96,6 +97,16 @@ class TraceList:
         return (self[i] for i in range(len(self)))
 
 
+def _locked(fn):
+    """one geometry call at a time per device context: upload -> kernels -> download of one cloud must not interleave
+    with another thread's on the same o3dpp_ctx (the C ABI's rule: calls on one ctx must not overlap)"""
+    @functools.wraps(fn)
+    def wrapper(self, *a, **kw):
+        with nat.context_lock(self._device):
+            return fn(self, *a, **kw)
+    return wrapper
+
+
 class DeviceCloud:
     def __init__(self, points=None, device=None):
         self._points = _EMPTY
@@ -103,6 +114,7 @@ class DeviceCloud:
         self._colors = _EMPTY
         self._device = int(os.environ.get("O3DPP_DEVICE", "0")) if device is None else int(device)
         self._resident = False       # inside resident(): device copy is authoritative
+        self._own_ctx = None         # inside resident(): a context of its own (the shared one serves every other cloud)
         self._stale = set()          # host attributes to refresh from the device (resident mode)
         self.seed = None             # RANSAC seed; None draws one from numpy's global RNG
         if points is not None:
@@ -168,7 +180,7 @@ class DeviceCloud:
 
     # ---- device plumbing
     def _ctx(self):
-        return nat.context(self._device)
+        return self._own_ctx if self._own_ctx is not None else nat.context(self._device)
 
     def _push_attr(self, attr, arr):
         ctx = self._ctx()
@@ -203,18 +215,26 @@ class DeviceCloud:
 
     @contextlib.contextmanager
     def resident(self):
-        """Keep the cloud on the GPU across several calls (no host round trip per call)."""
-        ctx = self._push(normals=True, colors=True)
-        self._resident = True
+        """Keep the cloud on the GPU across several calls (no host round trip per call).  The cloud gets a context of
+        its own for the duration: the process-wide context of the device keeps serving every other DeviceCloud and block,
+        so work on another cloud inside the `with` cannot replace this cloud's device copy."""
+        self._own_ctx = nat.Context(self._device)
         try:
+            self._push(normals=True, colors=True)
+            self._resident = True
             yield self
         finally:
-            for a in list(self._stale):
-                self._get({nat.ATTR_POINTS: "_points", nat.ATTR_NORMALS: "_normals", nat.ATTR_COLORS: "_colors"}[a], a)
-            self._resident = False
-            del ctx
+            try:
+                for a in list(self._stale):
+                    self._get({nat.ATTR_POINTS: "_points", nat.ATTR_NORMALS: "_normals", nat.ATTR_COLORS: "_colors"}[a], a)
+            finally:
+                self._resident = False
+                self._stale.clear()
+                ctx, self._own_ctx = self._own_ctx, None
+                ctx.close()
 
     # ---- the hot path (Open3D method names)
+    @_locked
     def transform(self, T):
         T = np.asarray(T, dtype=np.float64)
         if T.shape != (4, 4):
@@ -244,6 +264,7 @@ class DeviceCloud:
         T[:3, 3] = c - R @ c
         return self.transform(T)
 
+    @_locked
     def estimate_normals(self, search_param=None, fast_normal_computation=True):
         if not fast_normal_computation:
             raise NotImplementedError("only fast_normal_computation=True (Open3D's default) is implemented")
@@ -255,6 +276,7 @@ class DeviceCloud:
         self._pull(ctx, nat.ATTR_NORMALS)
         return self
 
+    @_locked
     def segment_plane(self, distance_threshold, ransac_n, num_iterations, probability=0.99999999, seed=None):
         """-> (plane float64[4], ascending inlier indices).  Open3D returns the indices as a
         list[int]; here it is an int32 ndarray (list(...) it if a list is needed)."""
@@ -269,13 +291,14 @@ class DeviceCloud:
                                        float(probability), sampler=nat.SAMPLER_PHILOX, seed=int(seed))
         return plane, inl
 
+    @_locked
     def voxel_down_sample_and_trace(self, voxel_size, min_bound=None, max_bound=None, approximate_class=False):
         """-> (DeviceCloud of voxel centroids, int32 (V,8) cubic-id matrix, TraceList).
-        Rows are in ascending (ix,iy,iz); Open3D's are in unordered_map order.  min_bound /
-        max_bound are accepted for signature compatibility; like the reference's only call
-        site (PointCloud.py:339-340) the cloud's own bounds are used."""
+        Rows are in ascending (ix,iy,iz); Open3D's are in unordered_map order.  min_bound is the grid
+        origin and max_bound enters the size check, as in Open3D's trace variant; None = the cloud's own
+        bounds, which is what the reference's only call site passes (PointCloud.py:339-340)."""
         ctx = self._push(normals=True, colors=True)
-        V = ctx.voxel(float(voxel_size))
+        V = ctx.voxel(float(voxel_size), min_bound, max_bound)
         n = ctx.size()
         fields = ["centroid", "cubic_id", "order", "seg"]
         hn, hc = ctx.has(nat.ATTR_NORMALS), ctx.has(nat.ATTR_COLORS)
@@ -295,12 +318,14 @@ class DeviceCloud:
     def voxel_down_sample(self, voxel_size):
         return self.voxel_down_sample_and_trace(voxel_size)[0]
 
-    def voxel_representatives(self, voxel_size):
+    @_locked
+    def voxel_representatives(self, voxel_size, min_bound=None, max_bound=None):
         """ascending `idxmat.max(1)`: the original indices reference PointCloud.py:341 keeps"""
         ctx = self._push(normals=False)
-        V = ctx.voxel(float(voxel_size))
+        V = ctx.voxel(float(voxel_size), min_bound, max_bound)
         return ctx.voxel_fetch(V, ctx.size(), ["rep_asc"])["rep_asc"]
 
+    @_locked
     def search_knn(self, knn=30, radius=None):
         """batched KDTreeFlann query of every point: (idx (n,knn) int32, d2, counts)"""
         ctx = self._push(normals=False)
@@ -308,6 +333,7 @@ class DeviceCloud:
         return ctx.knn(mode, int(knn), 0.0 if radius is None else float(radius))
 
     # ---- the callers either side of the path
+    @_locked
     def remove_statistical_outlier(self, nb_neighbors, std_ratio, print_progress=False):
         """-> (DeviceCloud of the kept points, kept indices ascending): Open3D RemoveStatisticalOutliers.
         The per-point mean neighbour distances come from the device (o3dpp_knn_mean_distance); the cloud
@@ -335,6 +361,7 @@ class DeviceCloud:
             out._colors = self._colors[idx]
         return out, idx
 
+    @_locked
     def zsplat(self, grid_size, x_min=None, x_max=None, y_min=None, y_max=None):
         """ZDepthViewer's scatter (reference processors.py:876-894) on the device: float32 (grid, grid) z of the
         last point per cell (NaN where empty) and that point's index.  Bounds default to the float32 min / max."""

@@ -10,6 +10,7 @@ selected round-robin per input mat (`cuda:{i % num_gpus}`, reference :206).
 import json
 import multiprocessing
 import os
+import weakref
 from typing import List, Optional
 
 import numpy as np
@@ -20,6 +21,18 @@ from .PointCloudMat import PointCloudMat, PointCloudMatInfo, PointCloudMatProces
 logger = print
 
 
+try:  # torch tensors are accepted as payload (CUDA tensors stay on the device), never required
+    import torch
+except Exception:  # pragma: no cover
+    torch = None
+
+_RES_KEY = "_o3dpp_resident"      # meta[_RES_KEY][i] = what the previous block of this run_once left on the device for mat i
+
+
+def _is_cuda_tensor(x):
+    return torch is not None and isinstance(x, torch.Tensor) and x.is_cuda
+
+
 def _xyz(pcd):
     """contiguous (N,3) view/copy of the position columns, dtype kept (f32 uploads as f32)"""
     a = pcd[:, :3]
@@ -28,9 +41,23 @@ def _xyz(pcd):
     return np.ascontiguousarray(a)
 
 
+class _OnDevice:
+    """the device copy a block left behind: valid while the array object is the one handed on and nothing else has
+    changed the points of that context (Context.generation)"""
+    __slots__ = ("ref", "ctx", "generation")
+
+    def __init__(self, arr, ctx):
+        self.ref, self.ctx, self.generation = weakref.ref(arr), ctx, ctx.generation
+
+
 class _DeviceBlock(PointCloudMatProcessor):
     """common part of the device blocks: one library context per GPU, created lazily in the
-    process that runs the block (so blocks survive `run_async`'s JSON round trip and fork)"""
+    process that runs the block (so blocks survive `run_async`'s JSON round trip and fork).
+
+    A frame is uploaded ONCE per run_once: the block that uploads (or changes) the points of mat i records it in
+    `meta`, and the next block that receives the very same array object finds the cloud already resident, as the
+    reference's blocks find the CUDA tensor NumpyToTorch made (reference processors.py:188-209, :651-663).  float32
+    mats travel as float32 (12 B/point); CUDA tensor mats are read and written in place through the *_dev calls."""
     multi_gpu: int = -1
 
     def _device(self, i):
@@ -45,8 +72,34 @@ class _DeviceBlock(PointCloudMatProcessor):
             return int(pin)
         return i % len(self.num_devices)
 
-    def _ctx(self, i):
+    def _ctx(self, i, pcd=None):
+        if _is_cuda_tensor(pcd):
+            return nat.context(pcd.device.index)
         return nat.context(self._device(i))
+
+    def _resident(self, i, pcd, meta):
+        """-> context of mat i whose points are pcd[:, :3] (uploaded unless the previous block left them there)"""
+        ctx = self._ctx(i, pcd)
+        h = meta.get(_RES_KEY, {}).get(i) if isinstance(meta, dict) else None
+        if h is not None and h.ref() is pcd and h.ctx is ctx and h.generation == ctx.generation and ctx.size() == len(pcd):
+            return ctx
+        if _is_cuda_tensor(pcd):
+            t = pcd[:, :3]
+            if t.dtype not in (torch.float32, torch.float64):
+                t = t.double()
+            t = t.contiguous()
+            torch.cuda.current_stream(pcd.device).synchronize()     # the library reads on its own stream
+            ctx.upload_dev(nat.ATTR_POINTS, t.data_ptr(), len(t), nat.F32 if t.dtype == torch.float32 else nat.F64)
+        else:
+            ctx.upload(nat.ATTR_POINTS, _xyz(pcd))
+        ctx.drop(nat.ATTR_NORMALS)
+        return ctx
+
+    @staticmethod
+    def _leave(i, arr, ctx, meta):
+        """record that ctx now holds arr[:, :3] as its points"""
+        if isinstance(meta, dict):
+            meta.setdefault(_RES_KEY, {})[i] = _OnDevice(arr, ctx)
 
 
 class Processors:
@@ -79,14 +132,25 @@ class Processors:
             for i, pcd in enumerate(pcds_data):
                 if i < len(self.input_shape_types) and self.input_shape_types[i].contains_normals():
                     continue
-                ctx = self._ctx(i)
-                ctx.upload(nat.ATTR_POINTS, _xyz(pcd))
-                ctx.drop(nat.ATTR_NORMALS)
+                ctx = self._resident(i, pcd, meta)
                 mode = nat.SEARCH_HYBRID if self.radius > 0 else nat.SEARCH_KNN
+                ctx.drop(nat.ATTR_NORMALS)
                 ctx.estimate_normals(mode, self.knn, self.radius)
-                out = np.empty((len(pcd), pcd.shape[1] + 3), np.float64)      # = np.hstack([pcd, normals]) without the temporaries
-                out[:, :pcd.shape[1]] = pcd
-                out[:, pcd.shape[1]:] = ctx.download(nat.ATTR_NORMALS)
+                D = pcd.shape[1]
+                if _is_cuda_tensor(pcd):                      # = torch.hstack([pcd, normals]) in float64, on the device
+                    out = torch.empty((len(pcd), D + 3), dtype=torch.float64, device=pcd.device)
+                    nrm = torch.empty((len(pcd), 3), dtype=torch.float64, device=pcd.device)
+                    ctx.download_dev(nat.ATTR_NORMALS, nrm.data_ptr(), nat.F64)
+                    out[:, :D] = pcd
+                    out[:, D:] = nrm
+                else:                                         # = np.hstack([pcd, normals]) (float64) without the temporaries
+                    out = np.empty((len(pcd), D + 3), np.float64)
+                    if D == 3:
+                        ctx.download_rows6(out)               # rows assembled on the device, one copy
+                    else:
+                        out[:, :D] = pcd
+                        out[:, D:] = ctx.download(nat.ATTR_NORMALS)
+                self._leave(i, out, ctx, meta)
                 res.append(out)
             return res
 
@@ -100,11 +164,10 @@ class Processors:
         def forward_raw(self, pcds_data, pcds_info=[], meta={}):
             res = []
             for i, pcd in enumerate(pcds_data):
-                ctx = self._ctx(i)
-                ctx.upload(nat.ATTR_POINTS, _xyz(pcd))
+                ctx = self._resident(i, pcd, meta)
                 V = ctx.voxel(self.voxel_size)
                 rep = ctx.voxel_fetch(V, len(pcd), ["rep"])["rep"]   # rows in ascending voxel key
-                res.append(pcd[rep])
+                res.append(pcd[torch.as_tensor(rep, device=pcd.device).long()] if _is_cuda_tensor(pcd) else pcd[rep])
             return res
 
     class PlaneDetection(_DeviceBlock):
@@ -125,27 +188,29 @@ class Processors:
             pcd.require_ndarray()
             self.best_planes.append([0., 0., 0., 0.])
 
-        def detect(self, i, pcd):
-            xyz = _xyz(pcd)
-            if self.z_lower is not None and self.z_upper is not None:
-                xyz = np.ascontiguousarray(xyz[(self.z_lower < xyz[:, 2]) & (xyz[:, 2] < self.z_upper)])
-            ctx = self._ctx(i)
-            ctx.upload(nat.ATTR_POINTS, xyz)
+        def detect(self, i, pcd, meta={}):
+            if self.z_lower is not None and self.z_upper is not None:      # z band: a subset, uploaded on its own
+                xyz = pcd[:, :3]
+                xyz = xyz[(self.z_lower < xyz[:, 2]) & (xyz[:, 2] < self.z_upper)]
+                ctx = self._resident(i, xyz, {})
+            else:
+                ctx = self._resident(i, pcd, meta)
+                self._leave(i, pcd, ctx, meta)             # segment_plane leaves the points as they are
             seed = self.seed if self.seed is not None else int(np.random.randint(0, 2**31 - 1))
             plane, _ = ctx.segment_plane(self.distance_threshold, 3, self.num_iterations,
                                          seed=seed + self._calls, fetch_inliers=False)
             n, d = plane[:3], plane[3]
-            if np.dot(n, np.zeros(3) - (-d * n)) < 0:   # normal towards the sensor origin
+            if np.dot(n, np.zeros(3) - (-d * n)) < 0:   # normal towards the sensor origin (reference :643-649)
                 plane = -plane
             return plane
 
         def forward_raw(self, pcds_data, pcds_info=[], meta={}):
             if self.voxel_size > 0.0:
-                pcds_data = Processors.VoxelDownsample(voxel_size=self.voxel_size, multi_gpu=self.multi_gpu).forward_raw(pcds_data)
+                pcds_data = Processors.VoxelDownsample(voxel_size=self.voxel_size, multi_gpu=self.multi_gpu).forward_raw(pcds_data, meta=meta)
             while len(self.best_planes) < len(pcds_data):
                 self.best_planes.append([0., 0., 0., 0.])
             for i, pcd in enumerate(pcds_data):
-                plane = self.detect(i, pcd)
+                plane = self.detect(i, pcd, meta)
                 self.best_planes[i] = (np.asarray(self.best_planes[i]) * (1.0 - self.alpha) + plane * self.alpha).tolist()
             self._calls += 1
             meta[self.uuid] = self.best_planes
@@ -161,23 +226,28 @@ class Processors:
 
         @staticmethod
         def rotation_matrix_from_vectors(vec1, vec2):
+            """Rodrigues rotation vec1 -> vec2 in the dtype of the inputs (reference :709-723)"""
+            dt = vec1.dtype
             a = vec1 / np.linalg.norm(vec1)
             b = vec2 / np.linalg.norm(vec2)
             v = np.cross(a, b)
+            if np.linalg.norm(v) < 1e-6:
+                return np.eye(3, dtype=dt)
+            c = np.dot(a, b)
             s = np.linalg.norm(v)
-            if s < 1e-6:
-                return np.eye(3)
-            K = np.array([[0, -v[2], v[1]], [v[2], 0, -v[0]], [-v[1], v[0], 0]])
-            return np.eye(3) + K + K @ K * ((1 - np.dot(a, b)) / (s ** 2))
+            kmat = np.array([[0, -v[2], v[1]], [v[2], 0, -v[0]], [-v[1], v[0], 0]], dtype=dt)
+            return np.eye(3, dtype=dt) + kmat + np.matmul(kmat, kmat) * ((1 - c) / (s ** 2))
 
         @classmethod
-        def plane_to_T(cls, plane):
+        def plane_to_T(cls, plane, dtype=np.float64):
+            """the 4x4 of rotate_to_plane (reference :725-739), built in the mat's dtype as the reference builds it"""
             a, b, c, d = plane
-            n = np.array([a, b, c], dtype=np.float64)
-            R = cls.rotation_matrix_from_vectors(n, np.array([0., 0., 1.]))
-            T = np.eye(4)
+            normal = np.array([a, b, c], dtype=dtype)
+            R = cls.rotation_matrix_from_vectors(normal, np.array([0, 0, 1], dtype=dtype))
+            point_on_plane = -d * normal / np.dot(normal, normal)
+            T = np.eye(4, dtype=dtype)
             T[:3, :3] = R
-            T[:3, 3] = -R @ (-d * n / np.dot(n, n))
+            T[:3, 3] = -np.matmul(R, point_on_plane)
             return T
 
         def forward_raw(self, pcds_data, pcds_info=[], meta={}):
@@ -185,14 +255,29 @@ class Processors:
             self.forward_T = [None] * len(pcds_data)
             res = []
             for i, pcd in enumerate(pcds_data):
-                T = self.plane_to_T(models[i])
-                ctx = self._ctx(i)
-                ctx.upload(nat.ATTR_POINTS, _xyz(pcd))
+                cuda = _is_cuda_tensor(pcd)
+                dt = np.dtype(str(pcd.dtype).replace("torch.", "")) if cuda else pcd.dtype
+                if dt not in (np.float32, np.float64):
+                    dt = np.dtype(np.float64)
+                T = self.plane_to_T(models[i], dt)
+                ctx = self._resident(i, pcd, meta)
                 ctx.drop(nat.ATTR_NORMALS)
-                ctx.transform(T)
-                out = np.empty_like(pcd)                                      # = np.hstack([xyz.astype(dtype), pcd[:, 3:]])
-                out[:, :3] = ctx.download(nat.ATTR_POINTS)
-                out[:, 3:] = pcd[:, 3:]
+                ctx.transform(T.astype(np.float64))      # T holds the mat-dtype values; the product runs in FP64 and is rounded once
+                if cuda:
+                    out = torch.empty_like(pcd)
+                    xyz = out if pcd.shape[1] == 3 else torch.empty((len(pcd), 3), dtype=pcd.dtype, device=pcd.device)
+                    ctx.download_dev(nat.ATTR_POINTS, xyz.data_ptr(), nat.F32 if dt == np.float32 else nat.F64)
+                    if pcd.shape[1] > 3:
+                        out[:, :3] = xyz
+                        out[:, 3:] = pcd[:, 3:]
+                else:
+                    out = np.empty(pcd.shape, dt)              # = np.hstack([xyz, pcd[:, 3:]]) in the mat's dtype
+                    if pcd.shape[1] == 3:
+                        ctx.download_as(nat.ATTR_POINTS, out)
+                    else:
+                        out[:, :3] = ctx.download_as(nat.ATTR_POINTS, np.empty((len(pcd), 3), dt))
+                        out[:, 3:] = pcd[:, 3:]
+                self._leave(i, out, ctx, meta)
                 res.append(out)
                 self.forward_T[i] = T.tolist()
             return res

@@ -101,13 +101,30 @@ static int vox_cmp(const void *pa, const void *pb)
  * out_oct  : n   int32 octant (cubic id) per ORIGINAL point
  * out_order: n   int32 original indices sorted by (voxel, index)
  * out_seg  : n+1 int64 segment offsets into out_order (first V+1 valid)      */
+/* min3 / max3 (nullable): the explicit grid origin and far corner of PointCloud::VoxelDownSampleAndTrace(voxel_size,
+ * min_bound, max_bound, ...) as the reference passes them (PointCloud.py:339-340); NULL = the cloud's own bounds, which
+ * is what the reference always passes.  The "trace" variant uses min_bound itself as the origin (no half-voxel shift)
+ * and max_bound only in the size check. */
+ORC_API int64_t orc_voxel_index_bounded(const double *pts, int64_t n, double voxel_size, const double *min3,
+                                        const double *max3, int32_t *out_vidx, int32_t *out_oct,
+                                        int32_t *out_order, int64_t *out_seg);
+
 ORC_API int64_t orc_voxel_index(const double *pts, int64_t n, double voxel_size,
                                 int32_t *out_vidx, int32_t *out_oct,
                                 int32_t *out_order, int64_t *out_seg)
 {
+    return orc_voxel_index_bounded(pts, n, voxel_size, NULL, NULL, out_vidx, out_oct, out_order, out_seg);
+}
+
+ORC_API int64_t orc_voxel_index_bounded(const double *pts, int64_t n, double voxel_size, const double *min3,
+                                        const double *max3, int32_t *out_vidx, int32_t *out_oct,
+                                        int32_t *out_order, int64_t *out_seg)
+{
     if (!(voxel_size > 0.0)) return -1;
     double mn[3], mx[3];
     orc_bounds(pts, n, mn, mx);
+    if (min3) { mn[0] = min3[0]; mn[1] = min3[1]; mn[2] = min3[2]; }
+    if (max3) { mx[0] = max3[0]; mx[1] = max3[1]; mx[2] = max3[2]; }
     double ext = mx[0] - mn[0];
     if (mx[1] - mn[1] > ext) ext = mx[1] - mn[1];
     if (mx[2] - mn[2] > ext) ext = mx[2] - mn[2];

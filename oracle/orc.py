@@ -52,17 +52,22 @@ def transform(pts, T, normals=None):
     return p, nrm
 
 
-def voxel_trace(pts, voxel_size, normals=None, colors=None):
-    """dict with rows in ascending voxel key (ix,iy,iz)."""
+def voxel_trace(pts, voxel_size, normals=None, colors=None, min_bound=None, max_bound=None):
+    """dict with rows in ascending voxel key (ix,iy,iz).  min_bound / max_bound: the explicit grid origin / far corner of
+    voxel_down_sample_and_trace(voxel_size, min_bound, max_bound) (reference PointCloud.py:339-340); None = own bounds."""
     p = _pts(pts)
     n = len(p)
     vidx = np.empty((n, 3), np.int32)
     octant = np.empty(n, np.int32)
     order = np.empty(n, np.int32)
     seg = np.empty(n + 1, np.int64)
-    V = lib().orc_voxel_index(p.ctypes.data_as(C.c_void_p), C.c_int64(n), C.c_double(voxel_size),
-                              vidx.ctypes.data_as(C.c_void_p), octant.ctypes.data_as(C.c_void_p),
-                              order.ctypes.data_as(C.c_void_p), seg.ctypes.data_as(C.c_void_p))
+    mnb = None if min_bound is None else np.ascontiguousarray(np.asarray(min_bound, dtype=np.float64).reshape(3))
+    mxb = None if max_bound is None else np.ascontiguousarray(np.asarray(max_bound, dtype=np.float64).reshape(3))
+    f = lib().orc_voxel_index_bounded
+    f.restype = C.c_int64
+    V = f(p.ctypes.data_as(C.c_void_p), C.c_int64(n), C.c_double(voxel_size), _opt(mnb), _opt(mxb),
+          vidx.ctypes.data_as(C.c_void_p), octant.ctypes.data_as(C.c_void_p),
+          order.ctypes.data_as(C.c_void_p), seg.ctypes.data_as(C.c_void_p))
     if V == -1:
         raise RuntimeError("voxel_size <= 0.")
     if V == -2:
