@@ -50,6 +50,12 @@ class _OnDevice:
         self.ref, self.ctx, self.generation = weakref.ref(arr), ctx, ctx.generation
 
 
+def _require_array(pcd):
+    """device blocks take host ndarrays or torch tensors (CUDA tensors stay on the device)"""
+    if not (pcd.is_ndarray() or pcd.is_torch_tensor()):
+        raise TypeError(f"Expected np.ndarray or torch.Tensor, got {type(pcd.data())}")
+
+
 class _DeviceBlock(PointCloudMatProcessor):
     """common part of the device blocks: one library context per GPU, created lazily in the
     process that runs the block (so blocks survive `run_async`'s JSON round trip and fork).
@@ -119,7 +125,7 @@ class Processors:
         radius: float = 0.0        # > 0 selects KDTreeSearchParamHybrid(radius, knn)
 
         def validate_pcd(self, idx, pcd: PointCloudMat):
-            pcd.require_ndarray()
+            _require_array(pcd)
             self.input_shape_types.append(pcd.shape_type)
 
         def build_out_mats(self, validated_pcds, converted_raw_pcds):
@@ -159,7 +165,7 @@ class Processors:
         voxel_size: float = 0.1
 
         def validate_pcd(self, idx, pcd: PointCloudMat):
-            pcd.require_ndarray()
+            _require_array(pcd)
 
         def forward_raw(self, pcds_data, pcds_info=[], meta={}):
             res = []
@@ -185,7 +191,7 @@ class Processors:
         _calls: int = 0
 
         def validate_pcd(self, idx, pcd: PointCloudMat):
-            pcd.require_ndarray()
+            _require_array(pcd)
             self.best_planes.append([0., 0., 0., 0.])
 
         def detect(self, i, pcd, meta={}):
@@ -222,7 +228,7 @@ class Processors:
         filter_pcd: bool = False
 
         def validate_pcd(self, idx, pcd):
-            pcd.require_ndarray()
+            _require_array(pcd)
 
         @staticmethod
         def rotation_matrix_from_vectors(vec1, vec2):

@@ -23,6 +23,8 @@ class _ShmArray(BaseModel):
     dtype_str: str = "float32"
     create: bool = False
     auto_del: bool = True
+    pin: bool = False          # page-lock the segment (o3dpp_host_register): uploads from it are direct DMA
+    _pinned: Any = None
     _shm: Any = None
     _arr: Any = None
     _seq: Any = None
@@ -39,6 +41,11 @@ class _ShmArray(BaseModel):
         self._arr = np.ndarray(tuple(self.array_shape), np.dtype(self.dtype_str), buffer=self._shm.buf, offset=_HDR)
         if self.create:
             self._seq[0] = 0
+        if self.pin and self._pinned is None:
+            from . import _native
+            whole = np.ndarray((self.shm_size,), np.uint8, buffer=self._shm.buf)
+            _native.host_register(whole)
+            self._pinned = whole
         return self
 
     def model_dump_json_dict(self):
@@ -48,6 +55,13 @@ class _ShmArray(BaseModel):
         return dict(shm_name=self.shm_name, array_shape=self.array_shape, dtype=self.dtype_str)
 
     def close(self):
+        if self._pinned is not None:
+            try:
+                from . import _native
+                _native.host_unregister(self._pinned)
+            except Exception:
+                pass
+            self._pinned = None
         shm, self._arr, self._seq, self._shm = self._shm, None, None, None
         if shm is not None:
             try:
@@ -99,14 +113,14 @@ class GeneralNumpySharedMemoryIO:
     DTYPE = "uint8"
 
     @classmethod
-    def reader(cls, stream_key, array_shape, dtype=None):
+    def reader(cls, stream_key, array_shape, dtype=None, pin=False):
         return _Reader(shm_name=stream_key.replace(":", "_"), array_shape=list(array_shape),
-                       dtype_str=np.dtype(dtype or cls.DTYPE).name, create=False).build_buffer()
+                       dtype_str=np.dtype(dtype or cls.DTYPE).name, create=False, pin=pin).build_buffer()
 
     @classmethod
-    def writer(cls, stream_key, array_shape, dtype=None):
+    def writer(cls, stream_key, array_shape, dtype=None, pin=False):
         return _Writer(shm_name=stream_key.replace(":", "_"), array_shape=list(array_shape),
-                       dtype_str=np.dtype(dtype or cls.DTYPE).name, create=True).build_buffer()
+                       dtype_str=np.dtype(dtype or cls.DTYPE).name, create=True, pin=pin).build_buffer()
 
 
 class NumpyUInt8SharedMemoryStreamIO(GeneralNumpySharedMemoryIO):
