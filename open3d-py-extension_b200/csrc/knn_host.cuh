@@ -31,22 +31,32 @@ static int launch_lane(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, K
         out.tier = c->g_tier.as<unsigned char>();
         CU_TRY(cudaMemsetAsync(out.tier, 0, (size_t)n, c->stream));
     }
-    size_t smem = (size_t)KL_WARPS * sizeof(KlWarpMem);
-    auto k1 = knn_lane_kernel<MODE>;
-    CU_TRY(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int64_t blocks = (gd.cnt[0] + KL_WARPS - 1) / KL_WARPS;
-    // rho = staging radius / part-box diagonal (0.44: measured optimum on the LiDAR-like scans).  A part whose grown box
-    // overflows the staging area retries with the radius shrunk (x shrink, up to max_shrink times), then is halved (never,
-    // at the default 12); gsplit = cell groups to scan beyond which an attempt is abandoned before scanning
-    // (10M, all three tiers: 48 -> 13.40 ms, 64 -> 13.23, 80 -> 13.30, 96 -> 13.42, 128 -> 13.47)
+    // rho = staging radius / home-box diagonal (0.44: measured optimum on the LiDAR-like scans).  A list longer than gsplit,
+    // or candidates that overflow the staging area, retry with the radius x shrink, up to max_shrink times
+    // (gsplit at 10M, all three tiers: 48 -> 13.40 ms, 64 -> 13.23, 80 -> 13.30, 96 -> 13.42, 128 -> 13.47)
     const KnnTune &t = c->tune;
     const float rho = t.rho > 0.f ? t.rho : 0.44f;
     const int max_shrink = t.max_shrink >= 0 && t.max_shrink <= 12 ? t.max_shrink : 12;
-    const int gsplit = t.gsplit >= 16 && t.gsplit <= KL_GMAX - 64 ? t.gsplit : 64;
+    const int gsplit = t.gsplit >= 16 && t.gsplit <= KS_GMAX - 64 ? t.gsplit : 64;
     const float shrink = t.shrink > 0.1f && t.shrink < 0.99f ? t.shrink : 0.7f;
+    // group lists (knn_groups_kernel) -> selection (knn_select_kernel)
+    KsGroups gr;
+    gr.pitch = ((gsplit + 31) / 32) * 32;
+    const int64_t ngr = gd.cnt[0];
+    O3_TRY(c->g_glist.ensure((size_t)ngr * gr.pitch * 4 + 64));
+    O3_TRY(c->g_gcnt.ensure((size_t)ngr * 3 + 64));
+    gr.list = c->g_glist.as<uint32_t>();
+    gr.cnt = c->g_gcnt.as<unsigned short>();
+    gr.tries = c->g_gcnt.as<unsigned char>() + (size_t)ngr * 2;
+    const size_t smem = sizeof(KsMem);
+    auto k1 = knn_select_kernel<MODE, KS_W>;
+    CU_TRY(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaEventRecord(c->ev[3], c->stream);
-    LAUNCH(c, k1, (int)blocks, KL_WARPS * 32, smem, gd, K, radius, rho, max_shrink, gsplit, shrink, out, capbuf);
-    O3_TRY(check_launch("knn_lane"));
+    LAUNCH(c, knn_groups_kernel<MODE>, (int)((ngr + KA_WARPS - 1) / KA_WARPS), KA_WARPS * 32, 0, gd, radius, rho, max_shrink, gsplit, shrink, gr);
+    O3_TRY(check_launch("knn_groups"));
+    cudaEventRecord(c->ev[7], c->stream);
+    LAUNCH(c, k1, (int)ngr, KS_W * 32, smem, gd, K, radius, rho, max_shrink, shrink, gr, out, capbuf);
+    O3_TRY(check_launch("knn_select"));
     cudaEventRecord(c->ev[4], c->stream);
     if (out.nx) {
         LAUNCH(c, knn_finish_kernel<MODE>, (int)((n + 127) / 128), 128, 0, gd, K, radius, out, capbuf);
@@ -154,6 +164,8 @@ static int search_impl(o3dpp_ctx *c, int mode, int K, double radius, bool want_n
     c->timings[2] = c->timings[3] = c->timings[6] = c->timings[7] = 0.0;
     if (fast) {
         float t1 = 0, t2 = 0, t3 = 0, tf = 0;
+        float tg = 0;
+        cudaEventElapsedTime(&tg, c->ev[3], c->ev[7]);      // group lists, part of t1
         cudaEventElapsedTime(&t1, c->ev[3], c->ev[4]);
         cudaEventElapsedTime(&tf, c->ev[4], c->ev[6]);
         cudaEventElapsedTime(&t2, c->ev[6], c->ev[5]);
@@ -164,9 +176,9 @@ static int search_impl(o3dpp_ctx *c, int mode, int K, double radius, bool want_n
         c->timings[6] = t3;     // compaction + tier 3
         if (c->want_stats && c->stats[16]) {
             double nq = (double)n, nw = (double)c->stats[16];
-            fprintf(stderr, "[o3dpp lane] n=%lld mode=%d K=%d tier1 %.3f ms, finish %.3f ms, tier2 %.3f ms, tier3 %.3f ms (tier2 %lld, tier3 %lld queries) | per warp: parts %.3f candidates %.1f "
+            fprintf(stderr, "[o3dpp lane] n=%lld mode=%d K=%d tier1 %.3f ms (lists %.3f), finish %.3f ms, tier2 %.3f ms, tier3 %.3f ms (tier2 %lld, tier3 %lld queries) | per warp: parts %.3f candidates %.1f "
                     "groups-scanned %.1f restages %.3f | fail per query: gap %.4f rho %.4f boundary %.4f count %.4f warp %.4f | split warps %.3f, kcycles per warp: single %.1f split %.1f\n", (long long)n, mode, K,
-                    t1, tf, t2, t3, (long long)c->timings[4], (long long)c->timings[5], c->stats[25] / nw, c->stats[17] / nw, c->stats[18] / nw, c->stats[24] / nw,
+                    t1, tg, tf, t2, t3, (long long)c->timings[4], (long long)c->timings[5], c->stats[25] / nw, c->stats[17] / nw, c->stats[18] / nw, c->stats[24] / nw,
                     c->stats[19] / nq, c->stats[20] / nq, c->stats[21] / nq, c->stats[22] / nq, c->stats[23] / nq,
                     c->stats[28] / nw, c->stats[26] / (nw - c->stats[28] + 1e-9) / 1e3, c->stats[27] / (c->stats[28] + 1e-9) / 1e3);
         }

@@ -21,7 +21,7 @@ for l in lines[start+1:]:
 import os
 src=open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),'open3d-py-extension_b200','csrc','knn_lane.cuh')).read().split('\n')
 def find(pat): return [i+1 for i,l in enumerate(src) if pat in l][0]
-marks=[('helpers',0),('gap',find('__device__ __forceinline__ float gap')),('collect',find('template <int LVL>')),('collect_levels',find('bool collect_levels')),('append+stage',find('void append(')),('kl_bin',find('int kl_bin(')),('sel-setup',find('KlAnswer kl_select')),('passA',find('// pass A')),('binscan',find('int c0 = 0, bstar')),('passC',find('// pass C:')),('passF',find('// pass F')),('certify',find('const float ubound')),('boundary-pick',find('const int need = K - c0')),('kernel-prolog',find('knn_lane_kernel(const GridDesc g')),('parts',find('int start = 0, len = 32')),('window',find('bool window = false')),('selcall',find('const int ncand =')),('finish-gather',find('if (inpart && valid)')),('stats',find('unsigned s1 = __reduce_add_sync')-2)]
+marks=[('helpers',0),('gap',find('__device__ __forceinline__ float gap')),('collect',find('template <int LVL>')),('collect_levels',find('bool collect_levels')),('append+stage',find('void append(')),('kl_bin',find('int kl_bin(')),('sel-setup',find('KlAnswer kl_select')),('passA',find('// pass A')),('binscan',find('int c0 = 0, bstar')),('passC',find('// pass C:')),('passF',find('// pass F')),('certify',find('const float ubound')),('boundary-pick',find('const int need = K - c0')),('kernel-prolog',find('knn_lane_kernel(const GridDesc g')),('parts',find('int start = 0, len = 32')),('window',find('bool window = false')),('selcall',find('const int ncand =')),('output',find('// OUTPUT: sorted positions')),('stats',find('unsigned s1 = __reduce_add_sync')-2)]
 marks.sort(key=lambda x:x[1])
 def bucket(k):
     if not k: return 'none'
