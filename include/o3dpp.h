@@ -213,6 +213,10 @@ O3DPP_API int o3dpp_inlier_moments(o3dpp_ctx *ctx, const double *centroid3, doub
  * o3dpp_estimate_normals (knn <= 32, KNN or hybrid): tells which queries near a slab cut need a wider halo */
 O3DPP_API int o3dpp_fetch_kth_bound(o3dpp_ctx *ctx, float *out);
 
+/* measured FP64 FMA throughput of the device in TFLOP/s (2 flop per FMA): the roofline the scoring pass of
+ * o3dpp_segment_plane (replaces the evaluation loop behind PointCloud.py:75-77) is reported against by bench.py */
+O3DPP_API int o3dpp_fp64_peak(o3dpp_ctx *ctx, double *tflops);
+
 /* ---- callers either side of the path */
 /* remove_statistical_outlier (PointCloud.py:370-372 -> Open3D RemoveStatisticalOutliers): out[i] = mean distance of
  * point i to its `knn` nearest points (itself included; summed in (d2, index) order), -1 if none */

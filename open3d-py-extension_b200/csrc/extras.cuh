@@ -102,3 +102,41 @@ static int zsplat_impl(o3dpp_ctx *c, int grid, double x0, double x1, double y0, 
     c->timings[0] = ms;
     return 0;
 }
+
+
+// ---- measured FP64 FMA peak of the device (segment_plane scoring is reported against it) ---------------
+// Eight independent chains of __fma_rn per thread (explicit intrinsic: the library is compiled -fmad=false), every SM full.
+__global__ void __launch_bounds__(256)
+fp64_peak_kernel(double *__restrict__ out, int iters, double a, double b)
+{
+    double v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = (double)(threadIdx.x + k);
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = __fma_rn(v[k], a, b);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += v[k];
+    if (s == 12345.678) out[0] = s;      // never true: keeps the chains alive
+}
+
+static int fp64_peak_impl(o3dpp_ctx *c, double *tflops)
+{
+    const int iters = 4096, blocks = c->sm_count * 8;
+    double *scratch = c->d_small.as<double>() + 1024;
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; ++rep) {
+        cudaEventRecord(c->ev[0], c->stream);
+        LAUNCH(c, fp64_peak_kernel, blocks, 256, 0, scratch, iters, 0.999999, 1e-9);
+        cudaEventRecord(c->ev[1], c->stream);
+        O3_TRY(check_launch("fp64_peak"));
+        CU_TRY(cudaStreamSynchronize(c->stream));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]);
+        if (rep && ms < best) best = ms;
+    }
+    *tflops = 2.0 * 8.0 * iters * 256.0 * blocks / (best * 1e-3) / 1e12;
+    return 0;
+}

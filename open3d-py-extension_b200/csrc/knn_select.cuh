@@ -28,7 +28,7 @@
 #include "knn_finish.cuh"
 
 #ifndef KS_W
-#define KS_W 2          // warps cooperating on one cell group (1 or 2)
+#define KS_W 1          // warps cooperating on one cell group (1 or 2; measured at 10 M: 1 -> 6.58 ms, 2 -> 7.69 ms: the barriers and the work both warps repeat cost more than the shorter critical path saves)
 #endif
 #ifndef KS_CAP
 #define KS_CAP 768      // staging slots per group, 2 KS_UNR of them padding
@@ -63,9 +63,13 @@
 #ifndef KA_WARPS
 #define KA_WARPS 8
 #endif
+#ifndef KS_LIST
+#define KS_LIST 56      // survivors of the threshold pass per query (16-bit staged slots): < K + KS_BND
+#endif
 #define KS_NOLIST 0xffffu
 
 static_assert(KS_W == 1 || KS_W == 2, "one or two warps per cell group");
+static_assert(32 - 1 + KS_BND < KS_LIST, "survivor list: K - 1 below the boundary bin + KS_BND inside it (K <= 32 on this path)");
 static_assert(KS_CAP % KS_UNR == 0 && KS_UNR % 2 == 0, "regions are padded to whole select iterations");
 
 // candidate s lives in half (s & 1) of record s >> 1
@@ -84,6 +88,13 @@ __device__ __forceinline__ float2 kl_d2pair(const float4 a, const float4 b, floa
     float2 dx = __fadd2_rn(make_float2(a.x, a.y), nqx), dy = __fadd2_rn(make_float2(a.z, a.w), nqy),
            dz = __fadd2_rn(make_float2(b.x, b.y), nqz);
     return __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
+}
+// d2 of staged slot s, the same three roundings as the packed form
+__device__ __forceinline__ float kl_d2slot(const float4 *cand, int s, float qx, float qy, float qz)
+{
+    const float *r = (const float *)(cand + (s & ~1)) + (s & 1);
+    float dx = __fadd_rn(r[0], -qx), dy = __fadd_rn(r[2], -qy), dz = __fadd_rn(r[4], -qz);
+    return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
 }
 // stores through 32-bit shared addresses: a running generic pointer costs a 64-bit add per step
 __device__ __forceinline__ void kl_sts16(unsigned a, unsigned short v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"(v) : "memory"); }
@@ -223,7 +234,7 @@ struct KsMem {
         struct { float d[KS_BND * 32]; unsigned short s[KS_BND * 32]; } bnd;      // [entry][lane], two-ended
     } u;
     union {
-        unsigned short nb[32 * 32];                                               // [j][lane] staged slots of the neighbours, two-ended
+        unsigned short nb[KS_LIST * 32];                                          // [j][lane] staged slots: survivors, then the neighbours; two-ended
         unsigned gl[KS_GMAX];                                                     // cell groups to scan (staging only)
     } v;
     unsigned short na[2][32], nbd[2][32];     // pass C, per warp and lane: neighbours / boundary entries collected
@@ -425,17 +436,17 @@ knn_select_kernel(const GridDesc g, int K, double radius, float rho_scale, int m
         const bool counted = bstar >= 0;
         if (takeall) bstar = KS_NB;
         const bool fits = takeall || (counted && cb <= KS_BND);  // else: a boundary bin too full for the list fails below
-        // float bits of the edges of b*: below tlo = neighbour, [tlo, thi) = boundary bin (bin 0 also holds everything below the range)
-        const int thi = fits ? ((takeall ? KS_NB : bstar + 1) + bbase) << KS_SHIFT : 0;
-        const int tlo = !fits ? 0 : (takeall ? thi : (bstar > 0 ? (bstar + bbase) << KS_SHIFT : (int)0x80000000));
+        const int thi = fits ? ((takeall ? KS_NB : bstar + 1) + bbase) << KS_SHIFT : 0;     // float bits of the upper edge of b*
         ks_sync<W>();     // the boundary lists alias the histograms: every lane of both warps has read its column
-        // pass C: the histogram guarantees c0 < K neighbours and cb <= KS_BND boundary entries over both warps, so the two-ended
-        // columns cannot meet; every rejected d2 is >= the upper edge of b*, which is all the certification needs to know
-        const unsigned na0 = (unsigned)__cvta_generic_to_shared(sm.v.nb + (w == 0 ? 0 : 31 * 32) + lane);
+        // pass C: d2 below the upper edge of b* -> the slot joins the survivor list: one compare, one predicated store and one
+        // predicated add per candidate.  The histogram guarantees c0 + cb < K + KS_BND <= KS_LIST survivors over both warps, so
+        // the two ends of the column cannot meet; every rejected d2 is >= the edge, which is all the certification needs
+        constexpr int LTOP = KS_LIST - 1;
+        const unsigned la0 = (unsigned)__cvta_generic_to_shared(sm.v.nb + (w == 0 ? 0 : LTOP * 32) + lane);
         const unsigned bd0 = (unsigned)__cvta_generic_to_shared(sm.u.bnd.d + (w == 0 ? 0 : (KS_BND - 1) * 32) + lane);
         const unsigned bs0 = (unsigned)__cvta_generic_to_shared(sm.u.bnd.s + (w == 0 ? 0 : (KS_BND - 1) * 32) + lane);
         const int stn = w == 0 ? 64 : -64, std_ = w == 0 ? 128 : -128;
-        unsigned naa = na0, bda = bd0, bsa = bs0;
+        unsigned la = la0;
         for (int s = sbeg; s < send; s += KS_UNR) {
             float4 cc[KS_UNR];
             float dd[KS_UNR];
@@ -447,23 +458,35 @@ knn_select_kernel(const GridDesc g, int K, double radius, float rho_scale, int m
                 dd[u] = d.x; dd[u + 1] = d.y;
             }
 #pragma unroll
-            for (int u = 0; u < KS_UNR; ++u) {
-                const int bits = __float_as_int(dd[u]);
-                if (bits < tlo) { kl_sts16(naa, (unsigned short)(s + u)); naa += stn; }
-                else if (bits < thi) { kl_sts32(bda, dd[u]); kl_sts16(bsa, (unsigned short)(s + u)); bda += std_; bsa += stn; }
-            }
+            for (int u = 0; u < KS_UNR; ++u)
+                if (__float_as_int(dd[u]) < thi) {
+                    kl_sts16(la, (unsigned short)(s + u));
+                    la += stn;
+                }
         }
+        // pass F: each warp looks at its own survivors again, compacting towards its own end of the column (the write index never
+        // passes the read index): bins below b* are neighbours, those of b* go to the boundary list with their d2
+        const int live = (int)(la - la0) / stn;
+        const int cmax = __reduce_max_sync(FULL, (unsigned)live);
+        const int beq = (takeall || !fits) ? -1 : bstar;
+        unsigned nba = la0, bda = bd0, bsa = bs0;
         {
-            const int mya = (int)(naa - na0) / stn, myb = (int)(bsa - bs0) / stn;
-            sm.na[w][lane] = (unsigned short)mya; sm.nbd[w][lane] = (unsigned short)myb;
+            const unsigned short *list = sm.v.nb + lane;
+            for (int e = 0; e < cmax; ++e) {
+                const int sl = e < live ? (int)list[(w == 0 ? e : LTOP - e) * 32] : 0;
+                const float d = kl_d2slot(cd, sl, qx, qy, qz);
+                const int b = e < live ? kl_bin(d, bbase) : KS_NB + 1;
+                if (b < bstar) { kl_sts16(nba, (unsigned short)sl); nba += stn; }
+                else if (b == beq) { kl_sts32(bda, d); kl_sts16(bsa, (unsigned short)sl); bda += std_; bsa += stn; }
+            }
+            sm.na[w][lane] = (unsigned short)((int)(nba - la0) / stn);
+            sm.nbd[w][lane] = (unsigned short)((int)(bsa - bs0) / stn);
         }
         ks_sync<W>();
         if (w == 0) {
             const int a0 = sm.na[0][lane], a1 = W > 1 ? sm.na[1][lane] : 0, b0 = sm.nbd[0][lane], b1 = W > 1 ? sm.nbd[1][lane] : 0;
-            float *bd = sm.u.bnd.d + lane;
-            unsigned short *bs = sm.u.bnd.s + lane;
-            const int nbnd = b0 + b1, btop = KS_BND - 1 + b0;      // entry e: warp 0's at e < b0, warp 1's from the top at btop - e
-#define KS_BE(e) (((e) < b0 ? (e) : btop - (e)) * 32)
+            float *bd = sm.u.bnd.d + lane;               // warp 0's entries at [0, b0), warp 1's at [KS_BND - b1, KS_BND)
+            const unsigned short *bs = sm.u.bnd.s + lane;
             const float ubound = U + kf_err(U, eA, eC) * 1.0001f;
             cn_up = a0; cn_dn = a1;
             why = 0;
@@ -479,24 +502,25 @@ knn_select_kernel(const GridDesc g, int K, double radius, float rho_scale, int m
                 capf = fminf(ubound, edge + kf_err(edge, eA, eC) * 1.0001f);
             } else {
                 const int need = K - c0;
-                unsigned nba = (unsigned)__cvta_generic_to_shared(sm.v.nb + a0 * 32 + lane);
+                unsigned nbw = (unsigned)__cvta_generic_to_shared(sm.v.nb + a0 * 32 + lane);
                 float a = 0.f;
                 for (int r = 0; r < need; ++r) {
                     float best = KF_HUGE;
                     int be = 0;
-                    for (int e = 0; e < nbnd; ++e) { float v = bd[KS_BE(e)]; if (v < best) { best = v; be = KS_BE(e); } }
+                    for (int e = 0; e < b0; ++e) { float v = bd[e * 32]; if (v < best) { best = v; be = e; } }
+                    if (W > 1) for (int e = KS_BND - b1; e < KS_BND; ++e) { float v = bd[e * 32]; if (v < best) { best = v; be = e; } }
                     a = best;
-                    kl_sts16(nba, bs[be]);
-                    nba += 64;
-                    bd[be] = KF_HUGE;
+                    kl_sts16(nbw, bs[be * 32]);
+                    nbw += 64;
+                    bd[be * 32] = KF_HUGE;
                 }
                 cn_up = a0 + need;
                 float rest = __int_as_float(thi);                            // no rejected candidate is closer
-                for (int e = 0; e < nbnd; ++e) rest = fminf(rest, bd[KS_BE(e)]);
-#undef KS_BE
+                for (int e = 0; e < b0; ++e) rest = fminf(rest, bd[e * 32]);
+                if (W > 1) for (int e = KS_BND - b1; e < KS_BND; ++e) rest = fminf(rest, bd[e * 32]);
                 const float ea = kf_err(a, eA, eC);
                 const bool c1 = rest - a > 2.0f * kf_err(rest, eA, eC), c2 = a + ea <= rho1f;
-                ok = c1 && c2 && a0 + a1 == c0 && nbnd == cb;
+                ok = c1 && c2 && a0 + a1 == c0 && b0 + b1 == cb;
                 capf = a + ea * 1.0001f;
                 if (!c1) why = 1; else if (!c2) why = 2;
             }
@@ -513,11 +537,14 @@ knn_select_kernel(const GridDesc g, int K, double radius, float rho_scale, int m
     if (__any_sync(FULL, put)) {
         uint32_t *dst = out.nbr + mypos;
         const int cn = cn_up + cn_dn;
-        for (int j = w; j < K; j += W)
-            if (put) {
-                const int e = j < cn_up ? j : 32 - cn_dn + (j - cn_up);
-                dst[(int64_t)j * out.nbr_pitch] = j < cn ? (uint32_t)kl_pos(sm.cand, sm.v.nb[e * 32 + lane]) : KNN_NONE;
-            }
+        const int shift = KS_LIST - cn;                   // entry of neighbour j: j below cn_up, else from the top of the column
+        const unsigned short *col = sm.v.nb + lane;
+        dst += (int64_t)w * out.nbr_pitch;
+        for (int j = w; j < K; j += W, dst += (int64_t)W * out.nbr_pitch) {
+            const int e = j < cn_up ? j : min(j + shift, KS_LIST - 1);
+            const uint32_t pos = j < cn ? (uint32_t)kl_pos(sm.cand, col[e * 32]) : KNN_NONE;
+            if (put) *dst = pos;
+        }
     }
     if (w == 0) {
         if (valid) {

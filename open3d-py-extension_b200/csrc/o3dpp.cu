@@ -407,6 +407,12 @@ O3DPP_API int o3dpp_knn_mean_distance(o3dpp_ctx *c, int knn, double *out)
     if (!out) return set_err(O3DPP_E_ARG, "null argument");
     return knn_mean_distance_impl(c, knn, out);
 }
+O3DPP_API int o3dpp_fp64_peak(o3dpp_ctx *c, double *tflops)
+{
+    CTX_CHECK(c);
+    if (!tflops) return set_err(O3DPP_E_ARG, "null argument");
+    return fp64_peak_impl(c, tflops);
+}
 O3DPP_API int o3dpp_zsplat(o3dpp_ctx *c, int grid_size, double x_min, double x_max, double y_min, double y_max, float *z_grid,
                            int32_t *last_index)
 {
