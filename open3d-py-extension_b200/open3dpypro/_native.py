@@ -33,7 +33,7 @@ SYMBOLS = [
     "o3dpp_select_inliers", "o3dpp_sample_philox", "o3dpp_planes_from_points", "o3dpp_score_planes",
     "o3dpp_plane_inliers", "o3dpp_inlier_moments", "o3dpp_fetch_kth_bound", "o3dpp_knn_mean_distance", "o3dpp_zsplat", "o3dpp_download_async",
     "o3dpp_set_option", "o3dpp_fetch_neighbors", "o3dpp_voxel_bounded", "o3dpp_download_as", "o3dpp_download_rows6",
-    "o3dpp_host_register", "o3dpp_host_unregister",
+    "o3dpp_host_register", "o3dpp_host_unregister", "o3dpp_fp64_peak",
 ]
 
 _lib = None
@@ -413,6 +413,12 @@ class Context:
         _check(lib().o3dpp_zsplat(self._h, C.c_int(g), C.c_double(x_min), C.c_double(x_max), C.c_double(y_min), C.c_double(y_max),
                                   _ptr(z), _ptr(last)))
         return z, last
+
+    def fp64_peak(self):
+        """measured FP64 FMA throughput of the device, TFLOP/s"""
+        v = C.c_double(0.0)
+        _check(lib().o3dpp_fp64_peak(self._h, C.byref(v)))
+        return v.value
 
     def kth_bound(self):
         """per point: upper bound of the squared distance to its k-th neighbour (last estimate_normals)"""
