@@ -8,9 +8,15 @@
 One step = one pass of the hot path over one scan: voxel_down_sample(0.1) (timed, reported under
 `stages_ms`, not part of the metric), then estimate_normals(KNN k=30) and segment_plane(0.05, 3,
 1000) on the full scan.  `value` = points / (t_normals + t_segment), inputs resident in HBM.
-`e2e` = the same two calls through the C ABI with page-locked HOST buffers: H2D of the float64
-(N,3) points, D2H of the float64 normals, the inlier list and the plane inside the timed region.
+`e2e` = the same two calls through the C ABI with page-locked HOST buffers: H2D of the float32
+(N,3) points (the scan is float32, as the block layer's mats are), D2H of the float64 normals, the
+inlier list and the plane inside the timed region.
 At N > 1 every rank owns its own scan (frame/scan sharding, no data-path collective): weak scaling.
+Beside the headline the same JSON line carries (BASELINE.json configs):
+  stages   transform / voxel_down_sample / segment_plane scoring against their own rooflines
+  c1       bunny chain (config 1), c2 = 1 M-point scan: transform + hybrid normals + segment_plane (config 2)
+  c4       256 frames x 131072 points through the processor blocks, frame f -> rank f mod G (config 4)
+  c5       (N > 1, or --c5) a 200 M-point scan sharded by spatial slab with NCCL halo exchange (config 5)
 `--impl reference` times the CPU oracle (a restatement of Open3D 0.19's algorithms, the reference's
 CPU path; the Open3D wheel itself is not installable here) on the host cores.
 """
@@ -33,6 +39,15 @@ import numpy as np  # noqa: E402
 METRIC = "Mpoints/s estimate_normals+segment_plane @10M pts"
 VOXEL, KNN, THR, RANSAC_N, ITERS = 0.1, 30, 0.05, 3, 1000
 ALGO_BYTES_PER_POINT_KNN = 384.0   # N*(12 + 12k + 12) at k = 30
+
+
+def c3_config(n):
+    """the workload description, byte-identical in both arms (the driver compares the two `config` objects)"""
+    return {"workload": "C3: synthetic 10M-point scan, estimate_normals(k=30)+segment_plane(0.05,3,1000)",
+            "points_per_gpu": int(n), "generator": "open3dpypro.synthetic.lidar_like(seed 1235 + rank), float32 values",
+            "sharding": "one scan per GPU, no data-path collective",
+            "l2": "inputs (240 MB FP64 planes per scan) exceed the 126 MB L2",
+            "timing": "ours: CUDA events on the library stream, max over ranks; reference: wall clock on the host cores"}
 
 
 def peaks():
@@ -175,26 +190,200 @@ def oracle_pass(pts, threads):
 def run_reference(args, rank, world):
     if rank != 0:
         return
-    from oracle import orc
     from open3dpypro.synthetic import lidar_like, SEED_C3
     threads = os.cpu_count() or 1
     n = min(args.points, args.ref_points)
     pts = lidar_like(n, SEED_C3)
-    for _ in range(min(args.warmup, 1)):
-        oracle_pass(pts[: max(n // 10, 1000)], threads)
+    warm_n = max(n // 10, 1000)
+    for _ in range(args.warmup):                      # every warm-up pass runs, on a tenth of the scan (a full pass takes seconds)
+        oracle_pass(pts[:warm_n], threads)
     ts = [oracle_pass(pts, threads) for _ in range(args.steps)]
     ms = 1e3 * sum(ts) / len(ts)
     val = n / (ms * 1e-3) / 1e6
-    sample = f"{n}-point scan from the same generator (seed {SEED_C3}), KNN k={KNN} normals + segment_plane({THR},{RANSAC_N},{ITERS}), OpenMP on all host threads"
+    sample = (f"{n}-point scan from the same generator (seed {SEED_C3}), KNN k={KNN} normals + segment_plane({THR},{RANSAC_N},{ITERS}), "
+              f"C oracle built -O3 -fopenmp, all {threads} host threads; warm-up passes on {warm_n} points")
     emit(({
         "impl": "reference", "metric": METRIC, "value": val, "unit": "Mpoints/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "C3: synthetic 10M-point scan, estimate_normals(k=30)+segment_plane(0.05,3,1000)",
-                   "points_per_step": n, "note": "CPU oracle = C restatement of Open3D 0.19 (wheel unavailable on this box)"},
+        "config": c3_config(n),
+        "note": "CPU oracle = C restatement of Open3D 0.19 (wheel unavailable on this box)",
         "cpu_baseline": {"value": val, "unit": "Mpoints/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "Mpoints/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
+
+
+
+# ---------------------------------------------------------------------------------------------- the other configs and stages
+def _max_over_ranks(vals, dist, local):
+    import torch
+    t = torch.tensor([float(v) for v in vals], dtype=torch.float64, device=f"cuda:{local}")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(v) for v in t.tolist()]
+
+
+def stage_rooflines(ctx, nat, N, pts32, med, peak):
+    """transform / voxel_down_sample / segment_plane scoring of the C3 scan against their own rooflines"""
+    T = np.eye(4)
+    c, s_ = np.cos(0.3), np.sin(0.3)
+    T[:2, :2] = [[c, -s_], [s_, c]]
+    T[:3, 3] = [1.0, -2.0, 0.5]
+    ctx.drop(nat.ATTR_NORMALS)
+    tt = []
+    for _ in range(5):
+        ctx.transform(T)
+        tt.append(ctx.timings()[0])
+    t_tr = statistics.median(tt[1:])
+    ctx.upload(nat.ATTR_POINTS, pts32)
+    mn, mx = ctx.bounds()
+    bits = sum(max(1, int(np.floor((mx[a] - mn[a]) / VOXEL)).bit_length()) for a in range(3))
+    P = (bits + 7) // 8
+    vox_bytes = (64 + 24 * P) * N
+    fma = ctx.fp64_peak()
+    flop = 8.0 * N * med["ransac_scored"]
+    tf = flop / (med["ransac_score"] * 1e-3) / 1e12 if med["ransac_score"] > 0 else 0.0
+    return {
+        "transform": {"ms": t_tr, "bytes_per_point": 48, "achieved_gbs": 48.0 * N / (t_tr * 1e-3) / 1e9, "frac_of_hbm_peak": 48.0 * N / (t_tr * 1e-3) / 1e9 / peak,
+                      "note": "affine T (last row 0 0 0 1): the w division is skipped bit-exactly; points only"},
+        "voxel_down_sample": {"ms": med["voxel"], "key_bits": bits, "radix_passes_of_8_bits": P, "algorithmic_bytes": vox_bytes,
+                              "achieved_gbs": vox_bytes / (med["voxel"] * 1e-3) / 1e9, "frac_of_hbm_peak": vox_bytes / (med["voxel"] * 1e-3) / 1e9 / peak},
+        "segment_plane_scoring": {"ms": med["ransac_score"], "hypotheses_scored": med["ransac_scored"], "flop": flop, "achieved_tflops": tf,
+                                  "fp64_fma_peak_tflops_measured": fma, "frac_of_fma_peak": tf / fma if fma > 0 else None,
+                                  "note": "8 unfused FP64 operations per (point, hypothesis): the reference's rounding forbids FMA, so 0.5 is the ceiling"},
+    }
+
+
+def run_c1(nat):
+    """config 1: the reference's bunny through the PointCloud API: voxel_down_sample + estimate_normals(k=30) + segment_plane"""
+    from open3dpypro.PointCloud import PointCloud
+    path = os.path.join(ROOT, "tests", "golden", "bunny_xyz_f32.npy")
+    if not os.path.exists(path):
+        return {"unavailable": "tests/golden/bunny_xyz_f32.npy missing"}
+    bunny = np.load(path).astype(np.float64)
+    ts = []
+    for _ in range(4):
+        t0 = time.perf_counter()
+        pc = PointCloud(bunny)
+        down = pc.voxel_down_sample(0.005)
+        pc.estimate_normals()
+        plane, inl = pc.segment_plane(0.01, 3, 450, seed=5)
+        ts.append((time.perf_counter() - t0) * 1e3)
+    return {"workload": "C1: data/bunny (35947 points) via open3dpypro.PointCloud: voxel_down_sample(0.005) + estimate_normals(k=30) + segment_plane(0.01,3,450)",
+            "ms_end_to_end_host_arrays": statistics.median(ts[1:]), "voxels": int(down.size()), "inliers": int(len(inl))}
+
+
+def run_c2(ctx, nat):
+    """config 2: 1 M-point scan, transform + estimate_normals(hybrid 0.5 / 30) + segment_plane(1000), device resident"""
+    from open3dpypro.synthetic import lidar_like, SEED_C2
+    n = 1_000_000
+    pts = lidar_like(n, SEED_C2, np.float32)
+    T = np.eye(4)
+    T[:3, 3] = [0.5, 0.25, -0.125]
+    rows = []
+    for _ in range(4):
+        ctx.upload(nat.ATTR_POINTS, pts)
+        ctx.drop(nat.ATTR_NORMALS)
+        ctx.transform(T)
+        t_tr = ctx.timings()[0]
+        ctx.estimate_normals(nat.SEARCH_HYBRID, KNN, 0.5)
+        tk = ctx.timings()
+        ctx.segment_plane(THR, RANSAC_N, ITERS, seed=1, fetch_inliers=False)
+        tsg = ctx.timings()
+        rows.append((t_tr, tk[0] + tk[1], tsg[0] + tsg[1] + tsg[2]))
+    t_tr, t_n, t_s = [statistics.median(r[i] for r in rows[1:]) for i in range(3)]
+    return {"workload": "C2: synthetic 1M-point scan: transform + estimate_normals(hybrid r=0.5, max_nn=30) + segment_plane(0.05,3,1000)",
+            "transform_ms": t_tr, "normals_ms": t_n, "segment_ms": t_s, "mpoints_per_s": n / ((t_tr + t_n + t_s) * 1e-3) / 1e6}
+
+
+def run_c4(rank, world, local, dist, barrier, frames_total=256, points=131072):
+    """config 4: frames through PointCloudMatProcessors.run_once (reference processors.py:1054-1074), frame f -> rank f mod G"""
+    from open3dpypro import sharding as sh
+    from open3dpypro.PointCloudMat import PointCloudMat, ShapeType
+    from open3dpypro.processors import Processors, PointCloudMatProcessors
+    from open3dpypro.synthetic import lidar_like
+    os.environ["O3DPP_DEVICE"] = str(local)
+    mine = sh.frames_of_rank(frames_total, rank, world)
+    distinct = 8
+    frames = {f: lidar_like(points, 2000 + f, np.float32) for f in range(distinct)}
+    det = Processors.PlaneDetection(distance_threshold=THR, num_iterations=ITERS, alpha=1.0, seed=7)
+    pipes = [Processors.CPUNormals(), det, Processors.PlaneNormalize(detection_uuid=det.uuid)]
+    mat = PointCloudMat(shape_type=ShapeType.XYZ).build(frames[0])
+    PointCloudMatProcessors.run_once([mat], {}, pipes, validate=True)
+    sec = 0.0
+    for rep in range(2):                      # first repetition = warm-up
+        barrier(); t0 = time.perf_counter()
+        for f in mine:
+            mat.unsafe_update_mat(frames[f % distinct])
+            PointCloudMatProcessors.run_once([mat], {}, pipes)
+        barrier(); sec = time.perf_counter() - t0
+    sec = _max_over_ranks([sec], dist, local)[0]
+    return {"workload": f"C4: {frames_total} frames x {points} points through CPUNormals -> PlaneDetection -> PlaneNormalize (run_once), frame f -> rank f mod G, host float32 frames in, host arrays out",
+            "frames": frames_total, "frames_per_s": frames_total / sec, "mpoints_per_s": frames_total * points / sec / 1e6,
+            "ms_per_frame_per_gpu": 1e3 * sec / max(len(mine), 1), "collectives_on_data_path": 0}
+
+
+def run_c5(ctx, nat, rank, world, local, dist, barrier, total):
+    """config 5: one scan of `total` points sharded by spatial slab: cuts + redistribution (all-to-all), voxel_down_sample with
+    the global origin, estimate_normals with a halo exchange (hybrid r=0.5/30 and pure KNN k=30), segment_plane with all-reduced
+    scores; device-resident bookkeeping (torch tensors, NCCL all_to_all_single / all_reduce over NVLink)"""
+    import torch
+    from open3dpypro import sharding as sh
+    from open3dpypro.synthetic import lidar_like, SEED_C5
+    part = torch.from_numpy(lidar_like(total // world, SEED_C5 + rank, np.float32)).cuda(local).double()
+    out = {"workload": f"C5: {total}-point scan sharded by spatial slab across {world} GPU(s): voxel_down_sample(0.1) + estimate_normals + segment_plane(0.05,3,1000)",
+           "points": total}
+    barrier(); t0 = time.perf_counter()
+    gmn, gmx = sh.global_bounds(part, world)
+    axis, cuts = sh.dev_slab_cuts(part, world, VOXEL, min_bound=gmn)
+    owned = sh.dev_redistribute(part, axis, cuts, rank, world, grid=(gmn, VOXEL))
+    barrier(); t_red = time.perf_counter() - t0
+    moved = int(len(part)) if world > 1 else 0          # upper bound of the rows this rank sends in the redistribution
+    del part
+    barrier(); t0 = time.perf_counter()
+    vres = sh.slab_voxel_down_sample(ctx, owned, rank, world, VOXEL, axis, cuts, gmn, gmx, fields=("rep",))
+    barrier(); t_vox = time.perf_counter() - t0
+    out["cut_redistribute_ms"] = _max_over_ranks([t_red * 1e3], dist, local)[0]
+    out["voxel"] = {"ms": _max_over_ranks([t_vox * 1e3], dist, local)[0], "voxels_total": vres["V_total"], "collectives": "all-reduce(min) of 6 doubles + all-gather of the row counts; no halo"}
+    out["redistribution_bytes_upper_bound_per_rank"] = moved * 24
+    for name, mode in (("hybrid", nat.SEARCH_HYBRID), ("knn", nat.SEARCH_KNN)):
+        rows = []
+        for step in range(2):                 # first pass = warm-up (buffer growth)
+            barrier(); t0 = time.perf_counter()
+            nrm, info = sh.dev_slab_estimate_normals(ctx, owned, axis, cuts, rank, world, mode, KNN, 0.5)
+            barrier(); t1 = time.perf_counter()
+            plane, m_loc, off, pinfo = sh.dev_slab_segment_plane(ctx, owned, rank, world, THR, RANSAC_N, ITERS, seed=1)
+            barrier(); t2 = time.perf_counter()
+            rows = [(t1 - t0) * 1e3, (t2 - t1) * 1e3]
+            del nrm
+        tn, ts_, halo, hb, ex = _max_over_ranks([rows[0], rows[1], info["halo_points"], info.get("halo_bytes", 0), info.get("exchange_ms", 0.0)], dist, local)
+        out[name] = {"normals_ms": tn, "segment_ms": ts_, "mpoints_per_s": total / ((tn + ts_) * 1e-3) / 1e6, "max_halo_points": int(halo),
+                     "max_halo_bytes_received": int(hb), "halo_exchange_ms": ex, "halo_width": info["halo_width"], "passes": info["passes"],
+                     "n_inliers": pinfo["n_inliers"], "max_owned_points": int(_max_over_ranks([len(owned)], dist, local)[0]),
+                     "collectives": "all_to_all_single (halo) + all-reduce of 3H sampled points, H counts + H error sums per 64-hypothesis batch, centroid, 6 moments"}
+    return out
+
+
+def copy_rates(ctx, nat, hin, hout, N):
+    """pure H2D / D2H rates of this rank's page-locked buffers (GB/s), to make host-side contention at N > 1 visible"""
+    t0 = time.perf_counter(); ctx.upload(nat.ATTR_POINTS, hin.array); ctx.synchronize(); t1 = time.perf_counter()
+    ctx.download(nat.ATTR_POINTS, hout.array); t2 = time.perf_counter()
+    return hin.array.nbytes / (t1 - t0) / 1e9, hout.array.nbytes / (t2 - t1) / 1e9
+
+
+def traffic_of_dominant_kernel():
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture, refused when the kernel source has
+    changed since (profiles/knn_traffic.json carries the sha256 of the source it was taken with)"""
+    import hashlib
+    path = os.path.join(ROOT, "profiles", "knn_traffic.json")
+    try:
+        d = json.load(open(path))
+        src = os.path.join(ROOT, "open3d-py-extension_b200", "csrc", d["source_file"])
+        if hashlib.sha256(open(src, "rb").read()).hexdigest()[:16] != d["source_sha16"]:
+            return None
+        return d.get("dram_bytes_per_launch")
+    except Exception:
+        return None
 
 
 _JSON_FD = None
@@ -231,6 +420,9 @@ def main():
     ap.add_argument("--no-token", dest="token", action="store_false",
                     help="end-to-end lanes: let the kernels of several scans share the GPU instead of taking turns")
     ap.add_argument("--inflight", type=int, default=2, help="scans in flight in the end-to-end measurement (1 = strictly serial)")
+    ap.add_argument("--c5", action="store_true", help="run the slab-sharded 200 M-point config at N = 1 too (always run at N > 1)")
+    ap.add_argument("--c5-points", type=int, default=200_000_000)
+    ap.add_argument("--no-extras", action="store_true", help="headline (C3) only: skip stages / c1 / c2 / c4 / c5")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -259,10 +451,10 @@ def main():
 
     numa = bind_to_gpu_numa_node(local) if world > 1 else None   # before the page-locked buffers are allocated
     N = args.points
-    pts = lidar_like(N, SEED_C3 + rank)          # every rank owns its own scan
+    pts = lidar_like(N, SEED_C3 + rank, np.float32)          # every rank owns its own scan; float32, as the block layer's mats
     ctx = nat.Context(local)
     stream = torch.cuda.ExternalStream(ctx.stream(), device=local)
-    hin = nat.PinnedArray((N, 3), np.float64)
+    hin = nat.PinnedArray((N, 3), np.float32)
     hin.array[...] = pts
     hout = nat.PinnedArray((N, 3), np.float64)
     hinl = nat.PinnedArray((N,), np.int32)       # page-locked home of the inlier list
@@ -283,7 +475,7 @@ def main():
         e[3].synchronize()
         stages.append({"voxel": e[0].elapsed_time(e[1]), "normals": e[1].elapsed_time(e[2]),
                        "segment": e[2].elapsed_time(e[3]), "grid_build": tk[0], "knn_kernel": tk[1],
-                       "knn_tier1": tk[2], "knn_tier2": tk[3], "knn_tier3": tk[6], "tier2_queries": tk[4], "tier3_queries": tk[5],
+                       "knn_tier1": tk[2], "knn_finish": tk[7], "knn_tier2": tk[3], "knn_tier3": tk[6], "tier2_queries": tk[4], "tier3_queries": tk[5],
                        "ransac_score": ts[1], "ransac_scored": ts[7], "V": V})
         return plane
 
@@ -294,7 +486,7 @@ def main():
 
     def e2e_step(lane=None):
         c, hi, ho, hx = lane or (ctx, hin, hout, hinl)
-        c.upload(nat.ATTR_POINTS, hi.array)            # H2D 24 B/point from page-locked memory
+        c.upload(nat.ATTR_POINTS, hi.array)            # H2D 12 B/point (float32) from page-locked memory
         if lane is None:                               # one scan at a time: the normals leave while segment_plane runs
             c.drop(nat.ATTR_NORMALS)
             c.estimate_normals(nat.SEARCH_KNN, KNN, 0.0)
@@ -343,7 +535,7 @@ def main():
         lanes = [(ctx, hin, hout, hinl)]
         for _ in range(args.inflight - 1):
             c2 = nat.Context(local)
-            hi2 = nat.PinnedArray((N, 3), np.float64)
+            hi2 = nat.PinnedArray((N, 3), np.float32)
             hi2.array[...] = pts
             lanes.append((c2, hi2, nat.PinnedArray((N, 3), np.float64), nat.PinnedArray((N,), np.int32)))
         for ln in lanes[1:]:
@@ -373,55 +565,73 @@ def main():
             assert np.array_equal(ho2.array, hout.array), "pipelined normals differ from the serial result"
             hi2.free(); ho2.free(); hx2.free(); c2.close()
     n_inl = int(len(inl))
+    h2d_gbs, d2h_gbs = copy_rates(ctx, nat, hin, hout, N)
+    rates = torch.tensor([h2d_gbs, d2h_gbs], dtype=torch.float64, device=f"cuda:{local}")
+    if dist is not None:
+        dist.all_reduce(rates, op=dist.ReduceOp.MIN)
+    h2d_gbs, d2h_gbs = [float(v) for v in rates.tolist()]
 
     tm = torch.tensor([t_metric, t_step, t_e2e, t_e2e_serial], dtype=torch.float64, device=f"cuda:{local}")
     if dist is not None:
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
     t_metric, t_step, t_e2e, t_e2e_serial = [float(v) for v in tm.tolist()]
 
+    peak, peak_src = peaks()
+    med = {k: statistics.median(s[k] for s in stages) for k in stages[0]}
+    extras = {}
+    if not args.no_extras:
+        ctx.upload(nat.ATTR_POINTS, pts)
+        if rank == 0:
+            extras["stages"] = stage_rooflines(ctx, nat, N, pts, med, peak)
+            extras["c1"] = run_c1(nat)
+            extras["c2"] = run_c2(ctx, nat)
+        hin.free(); hout.free(); hinl.free()
+        hin = hout = hinl = None
+        extras["c4"] = run_c4(rank, world, local, dist, barrier)
+        if world > 1 or args.c5:
+            extras["c5"] = run_c5(ctx, nat, rank, world, local, dist, barrier, args.c5_points)
+        else:
+            extras["c5"] = {"skipped": "runs at N > 1 (the driver's scaling run) or with --c5: generating the 200 M-point scan on one host process takes minutes"}
+
     if rank == 0:
-        peak, peak_src = peaks()
         knn_ms = sum(s["knn_kernel"] for s in stages) / len(stages)
         achieved = ALGO_BYTES_PER_POINT_KNN * N / (knn_ms * 1e-3) / 1e9
-        med = {k: statistics.median(s[k] for s in stages) for k in stages[0]}
         out = {
             "metric": METRIC, "value": world * N / (t_metric * 1e-3) / 1e6, "unit": "Mpoints/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_metric, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "C3: synthetic 10M-point scan, estimate_normals(k=30)+segment_plane(0.05,3,1000)"
-                                   " (voxel_down_sample(0.1) timed beside it)",
-                       "points_per_gpu": N, "sharding": "one scan per GPU, no data-path collective",
-                       "l2": "inputs (240 MB FP64 planes per scan) exceed the 126 MB L2",
-                       "timing": "CUDA events on the library stream; max over ranks",
-                       "numa_node_of_rank0": numa},
-            "stages_ms": med, "chain_ms_per_step": t_step,
+            "config": c3_config(N),
+            "numa_node_of_rank0": numa, "numa_note": None if numa is not None or world == 1 else "the box exposes no PCI/NUMA topology (/sys/bus/pci/.../numa_node absent or -1): nothing to bind to",
+            "stages_ms": med, "chain_ms_per_step": t_step, "stages_ms_note": "voxel_down_sample(0.1) is timed beside the metric, not inside it",
             "e2e": {"value": world * N / (t_e2e * 1e-3) / 1e6, "unit": "Mpoints/s", "ms_per_step": t_e2e,
                     "scans_in_flight": args.inflight, "serial_value": world * N / (t_e2e_serial * 1e-3) / 1e6,
                     "serial_ms_per_step": t_e2e_serial,
-                    "h2d_bytes_per_step": 24 * N, "d2h_bytes_per_step": 24 * N + 4 * n_inl + 32},
+                    "h2d_bytes_per_step": 12 * N, "d2h_bytes_per_step": 24 * N + 4 * n_inl + 32,
+                    "min_rank_h2d_gbs": h2d_gbs, "min_rank_d2h_gbs": d2h_gbs},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "knn_lane_kernel (tier 1) + knn_range_kernel + knn_exact_kernel: the whole neighbour search of one "
-                                                        "estimate_normals call, tiers 2 and 3 included in kernel_ms", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "hbm", "kernel": "knn_select_kernel (dominant) + knn_groups_kernel + knn_finish_kernel + knn_range_kernel + knn_exact_kernel: the whole "
+                                                        "neighbour search of one estimate_normals call, every tier and the finish included in kernel_ms", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": ALGO_BYTES_PER_POINT_KNN * N, "kernel_ms": knn_ms},
             "clocks": clocks,
         }
+        out.update(extras)
         if not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             n = min(N, args.ref_points)
             sec = oracle_pass(lidar_like(n, SEED_C3), threads)
+            n1 = min(n, 400_000)
+            sec1 = oracle_pass(lidar_like(n1, SEED_C3), 1)
             out["cpu_baseline"] = {"value": n / sec / 1e6, "unit": "Mpoints/s", "cores": threads, "kind": "port",
+                                   "value_1_thread": n1 / sec1 / 1e6,
                                    "sample": f"one pass over a {n}-point scan of the same generator ({sec:.1f} s), "
-                                             f"C oracle (Open3D 0.19 restatement), OpenMP on all host threads"}
-        traffic = os.path.join(ROOT, "profiles", "knn_traffic.json")
-        if os.path.exists(traffic):
-            try:
-                out["roofline"]["traffic"] = json.load(open(traffic)).get("dram_bytes_per_launch")
-            except Exception:
-                pass
+                                             f"C oracle (Open3D 0.19 restatement, -O3 -fopenmp), all host threads; 1-thread figure on {n1} points ({sec1:.1f} s)"}
+        out["roofline"]["traffic"] = traffic_of_dominant_kernel()
+        out["roofline"]["traffic_kernel"] = "knn_select_kernel, one ncu --set full capture (profiles/knn_traffic.json); null when the kernel source changed since"
         emit(out)
-    hin.free()
-    hout.free()
+    for b in (hin, hout, hinl):
+        if b is not None:
+            b.free()
     ctx.close()
     if dist is not None:
         dist.destroy_process_group()

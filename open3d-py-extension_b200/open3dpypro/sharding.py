@@ -95,8 +95,20 @@ def slab_cuts(points: np.ndarray, world: int, voxel_size: float, min_bound: Opti
     return axis, np.maximum.accumulate(np.asarray(cuts))
 
 
-def slab_of(points: np.ndarray, axis: int, cuts: Sequence[float]) -> np.ndarray:
-    """owner rank of every point: cuts[r] <= x < cuts[r+1]"""
+def cut_voxel_indices(cuts: Sequence[float], axis: int, min_bound, voxel_size: float) -> np.ndarray:
+    """voxel index along `axis` of every inner cut plane (slab_cuts puts them at min_bound + k * voxel_size)"""
+    inner = np.asarray(cuts, dtype=np.float64)[1:-1]
+    return np.rint((inner - float(np.asarray(min_bound)[axis])) / float(voxel_size)).astype(np.int64)
+
+
+def slab_of(points: np.ndarray, axis: int, cuts: Sequence[float], grid=None) -> np.ndarray:
+    """owner rank of every point: cuts[r] <= x < cuts[r+1].  grid = (min_bound, voxel_size): ownership by the voxel
+    index floor((x - min_bound) / voxel_size), the very expression voxel_down_sample keys with, so that no voxel can
+    straddle two ranks even when x sits within a rounding error of a cut plane."""
+    if grid is not None:
+        mn, vs = grid
+        ia = np.floor((points[:, axis] - float(np.asarray(mn)[axis])) / float(vs)).astype(np.int64)
+        return np.clip(np.searchsorted(cut_voxel_indices(cuts, axis, mn, vs), ia, side="right"), 0, len(cuts) - 2)
     return np.clip(np.searchsorted(np.asarray(cuts)[1:-1], points[:, axis], side="right"), 0, len(cuts) - 2)
 
 
@@ -148,13 +160,13 @@ def all_to_all_rows(send: Sequence[np.ndarray], rank: int, world: int, group=Non
     return [t.cpu().numpy() for t in ins]
 
 
-def redistribute(part: np.ndarray, axis: int, cuts: Sequence[float], rank: int, world: int, group=None) -> np.ndarray:
+def redistribute(part: np.ndarray, axis: int, cuts: Sequence[float], rank: int, world: int, group=None, grid=None) -> np.ndarray:
     """every rank holds an arbitrary part of the scan; afterwards it holds the points of its own slab
-    (rank-major, original order inside every source block).  One all-to-all."""
+    (rank-major, original order inside every source block).  One all-to-all.  grid: see slab_of."""
     part = np.asarray(part, dtype=np.float64).reshape(-1, 3)
     if world == 1:
         return part
-    owner = slab_of(part, axis, cuts)
+    owner = slab_of(part, axis, cuts, grid)
     got = all_to_all_rows([part[owner == r] for r in range(world)], rank, world, group)
     return np.concatenate(got, 0)
 
@@ -357,6 +369,97 @@ def slab_segment_plane(ctx, owned: np.ndarray, rank: int, world: int, distance_t
                                 "counts": counts, "samples": samples}
 
 
+# ---------------------------------------------------------------------------------- slab-sharded voxel_down_sample
+def global_bounds(points, world: int, group=None) -> Tuple[np.ndarray, np.ndarray]:
+    """(min_bound, max_bound) of the whole scan: one all-reduce(min) of 6 doubles.
+    `points`: this rank's part, a host array or a CUDA tensor."""
+    import torch
+    import torch.distributed as dist
+    if hasattr(points, "is_cuda"):
+        big = torch.full((3,), float("inf"), dtype=torch.float64, device=points.device)
+        mn = points.min(0).values.double() if len(points) else big
+        mx = points.max(0).values.double() if len(points) else -big
+        t = torch.cat([mn, -mx])
+    else:
+        p = np.asarray(points, dtype=np.float64)
+        mn = p.min(0) if len(p) else np.full(3, np.inf)
+        mx = p.max(0) if len(p) else np.full(3, -np.inf)
+        t = torch.from_numpy(np.concatenate([mn, -mx]))
+    if world > 1 and dist.is_initialized():
+        t = t.to(_dev(group))
+        dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
+    t = t.cpu().numpy()
+    return t[:3].copy(), -t[3:]
+
+
+def slab_voxel_down_sample(ctx, owned, rank: int, world: int, voxel_size: float, axis: int, cuts, min_bound, max_bound,
+                           group=None, fields=("rep", "count", "centroid")):
+    """voxel_down_sample_and_trace of a scan sharded by slab (reference call: PointCloud.py:338-341, which passes the
+    scan's min/max bound explicitly): every rank runs o3dpp_voxel_bounded on its own points with the GLOBAL bounds, so its
+    voxel keys are the whole scan's.  The cuts lie on voxel planes and ownership is by voxel index (redistribute(grid=)),
+    so no voxel straddles two ranks: no halo, no merge.  Collectives: one all-gather of the row counts.
+    -> dict: V (local rows), V_total, row_offset (rows of the lower ranks), keys (V,3) int64 voxel indices, the fetched
+    `fields` (rep indexes this rank's `owned`), globally_ordered (rank-major concatenation is the scan's ascending
+    (ix,iy,iz) order iff the slabs cut the most significant axis, x; gather_voxel_rows sorts otherwise).
+    `owned`: host (n,3) array or CUDA tensor."""
+    import torch
+    import torch.distributed as dist
+    from . import _native as nat
+    mn = np.asarray(min_bound, dtype=np.float64).reshape(3)
+    mx = np.asarray(max_bound, dtype=np.float64).reshape(3)
+    n = len(owned)
+    if hasattr(owned, "is_cuda"):
+        t = owned.contiguous()
+        _sync_torch()
+        ctx.upload_dev(nat.ATTR_POINTS, t.data_ptr(), n, nat.F32 if t.dtype == torch.float32 else nat.F64)
+    else:
+        ctx.upload(nat.ATTR_POINTS, owned)
+    ctx.drop(nat.ATTR_NORMALS)
+    V = ctx.voxel(float(voxel_size), mn, mx) if n else 0
+    want = tuple(dict.fromkeys(tuple(fields) + ("rep",)))
+    res = ctx.voxel_fetch(V, n, list(want)) if n else {k: np.empty((0,) + ((3,) if k == "centroid" else ()), np.float64 if k == "centroid" else np.int32) for k in want}
+    rep = res["rep"]
+    rp = owned[torch.as_tensor(rep, device=owned.device).long()].double().cpu().numpy() if hasattr(owned, "is_cuda") else np.asarray(owned, dtype=np.float64)[rep]
+    keys = np.floor((rp - mn) / float(voxel_size)).astype(np.int64)           # FP64 subtract, divide, floor: the device's expression
+    if V:
+        k = cut_voxel_indices(cuts, axis, mn, voxel_size)
+        lo = k[rank - 1] if rank > 0 else np.iinfo(np.int64).min
+        hi = k[rank] if rank < world - 1 else np.iinfo(np.int64).max
+        if keys[:, axis].min() < lo or keys[:, axis].max() >= hi:
+            raise ValueError("a voxel straddles a slab cut: redistribute the scan with grid=(min_bound, voxel_size)")
+    counts = [V]
+    if world > 1 and dist.is_initialized():
+        tv = torch.tensor([V], dtype=torch.int64, device=_dev(group))
+        parts = [torch.empty_like(tv) for _ in range(world)]
+        dist.all_gather(parts, tv, group=group)
+        counts = [int(p[0]) for p in parts]
+    out = dict(res)
+    out.update(V=V, V_total=int(sum(counts)), row_offset=int(sum(counts[:rank])), keys=keys, globally_ordered=(axis == 0 or world == 1))
+    return out
+
+
+def gather_voxel_rows(res: dict, rank: int, world: int, group=None) -> dict:
+    """all ranks' voxel rows (keys, count, centroid) on every rank, in the scan's ascending (ix,iy,iz) order"""
+    import torch
+    import torch.distributed as dist
+    cols = np.concatenate([res["keys"].astype(np.float64), np.asarray(res["count"], dtype=np.float64).reshape(-1, 1),
+                           np.asarray(res["centroid"], dtype=np.float64).reshape(-1, 3)], 1) if res["V"] else np.empty((0, 7))
+    if world > 1 and dist.is_initialized():
+        dev = _dev(group)
+        nloc = torch.tensor([len(cols)], dtype=torch.int64, device=dev)
+        ns = [torch.empty_like(nloc) for _ in range(world)]
+        dist.all_gather(ns, nloc, group=group)
+        ns = [int(v[0]) for v in ns]
+        buf = torch.zeros((max(ns + [1]), 7), dtype=torch.float64, device=dev)
+        buf[: len(cols)] = torch.from_numpy(cols).to(dev)
+        parts = [torch.empty_like(buf) for _ in range(world)]
+        dist.all_gather(parts, buf, group=group)
+        cols = np.concatenate([parts[r][: ns[r]].cpu().numpy() for r in range(world)], 0)
+    keys = cols[:, :3].astype(np.int64)
+    order = np.lexsort((keys[:, 2], keys[:, 1], keys[:, 0]))
+    return dict(keys=keys[order], count=cols[order, 3].astype(np.int32), centroid=cols[order, 4:7].copy(), V_total=len(cols))
+
+
 # ---------------------------------------------------------------------------------- the same, device resident
 # torch CUDA tensors in, torch CUDA tensors out: ownership, halo selection and the exchanges run on the GPU
 # (NCCL all_to_all_single over NVLink) and the library reads / writes the tensors in place
@@ -412,12 +515,18 @@ def _dev_all_to_all_rows(send, in_splits, world: int, group=None):
     return recv, out_splits
 
 
-def dev_redistribute(part, axis: int, cuts, rank: int, world: int, group=None):
+def dev_redistribute(part, axis: int, cuts, rank: int, world: int, group=None, grid=None):
     import torch
     if world == 1:
         return part
-    inner = torch.as_tensor(np.asarray(cuts)[1:-1], dtype=part.dtype, device=part.device)
-    owner = torch.bucketize(part[:, axis].contiguous(), inner, right=True).clamp_(0, world - 1)
+    if grid is not None:       # ownership by voxel index (see slab_of)
+        mn, vs = grid
+        ia = torch.floor((part[:, axis] - float(np.asarray(mn)[axis])) / float(vs)).long()
+        inner = torch.as_tensor(cut_voxel_indices(cuts, axis, mn, vs), dtype=torch.int64, device=part.device)
+        owner = torch.bucketize(ia, inner, right=True).clamp_(0, world - 1)
+    else:
+        inner = torch.as_tensor(np.asarray(cuts)[1:-1], dtype=part.dtype, device=part.device)
+        owner = torch.bucketize(part[:, axis].contiguous(), inner, right=True).clamp_(0, world - 1)
     order = torch.argsort(owner, stable=True)
     counts = torch.bincount(owner, minlength=world).tolist()
     recv, _ = _dev_all_to_all_rows(part[order], counts, world, group)
@@ -479,8 +588,13 @@ def dev_slab_estimate_normals(ctx, owned, axis: int, cuts, rank: int, world: int
             halo_w = float(_allreduce(np.array([span]), "sum", group)[0]) + 1.0
     else:
         halo_w = float(radius) if world > 1 else 0.0
+    import time
+    _sync_torch()
+    t0 = time.perf_counter()
     halo = dev_exchange_halo(owned, axis, cuts, rank, world, halo_w, group)
-    info.update(halo_width=halo_w, halo_points=int(len(halo)))
+    _sync_torch()
+    info.update(halo_width=halo_w, halo_points=int(len(halo)), halo_bytes=int(len(halo)) * 24,
+                exchange_ms=(time.perf_counter() - t0) * 1e3)
     loc = run(torch.cat([owned, halo], 0) if len(halo) else owned)
     out = torch.empty((len(loc), 3), dtype=torch.float64, device=owned.device)
     if len(loc):

@@ -107,6 +107,14 @@ def _worker(rank, world, port, q):
             out[f"info{mode}"] = info
         plane, inl, off, info = sh.slab_segment_plane(ctx, owned, rank, world, 0.05, 3, 400, seed=3, n_use=len(owned))
         out.update(plane=plane, inl=inl, off=off, best_iter=info["best_iter"], n_inliers=info["n_inliers"])
+        # voxel_down_sample across the slabs: global bounds as the grid origin, ownership by voxel index
+        gmn, gmx = sh.global_bounds(part, world)
+        vaxis, vcuts = sh.slab_cuts(part, world, 0.1, min_bound=gmn)
+        mine_v = sh.redistribute(part, vaxis, vcuts, rank, world, grid=(gmn, 0.1))
+        vres = sh.slab_voxel_down_sample(ctx, mine_v, rank, world, 0.1, vaxis, vcuts, gmn, gmx)
+        assert np.array_equal(mine_v[vres["rep"]].shape, (vres["V"], 3))
+        out["vox"] = sh.gather_voxel_rows(vres, rank, world)
+        out["vox_local"] = (vres["V"], vres["row_offset"], vres["V_total"], vaxis)
         ctx.close()
         q.put((rank, "ok", out))
     except Exception:   # noqa: BLE001
@@ -151,3 +159,18 @@ def test_world2_slabs_equal_single_context(ctx):
     assert np.array_equal(ginl, inl)
     assert o0["n_inliers"] == len(inl)
     assert np.abs(o0["plane"] - plane).max() < 1e-9 and np.array_equal(o0["plane"], o1["plane"])
+    # sharded voxel_down_sample == the single-context call == the oracle, rows in ascending (ix,iy,iz)
+    from oracle import orc
+    from open3dpypro.synthetic import lidar_like
+    pts = lidar_like(120_000, 31)
+    ctx.upload(nat.ATTR_POINTS, pts)
+    V = ctx.voxel(0.1)
+    one = ctx.voxel_fetch(V, len(pts), ["count", "centroid"])
+    ref = orc.voxel_trace(pts, 0.1)
+    for o in (o0, o1):
+        vx = o["vox"]
+        assert vx["V_total"] == V == ref["V"]
+        assert np.array_equal(vx["keys"], ref["keys"]) and np.array_equal(vx["count"], ref["count"]) and np.array_equal(vx["count"], one["count"])
+        assert np.abs(vx["centroid"] - ref["centroid"]).max() <= 1e-5 * np.abs(ref["centroid"]).max()      # north_star bar; sums differ in order only
+        assert np.abs(vx["centroid"] - one["centroid"]).max() <= 1e-12 * np.abs(ref["centroid"]).max()
+    assert o0["vox_local"][0] + o1["vox_local"][0] == V and o0["vox_local"][1] == 0 and o1["vox_local"][1] == o0["vox_local"][0]

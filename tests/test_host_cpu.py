@@ -245,6 +245,19 @@ def _gloo_worker(rank, world, port, q):
         for h in (0, 7, 15):
             c, e = orc.score_plane(pts, orc.plane_model(pts, samples[h]), 0.05)
             assert gc[h] == c and abs(ge[h] - e) <= 1e-9 * max(1.0, abs(e))
+        # voxel_down_sample across slabs: global bounds, ownership by voxel index, rows of all ranks in
+        # the scan's ascending key order == the oracle's rows (the per-rank voxel call is emulated by the oracle here; the
+        # device call is exercised at world 2 in tests/test_gpu_sharded.py)
+        gmn, gmx = sh.global_bounds(part, world)
+        assert np.array_equal(gmn, pts.min(0)) and np.array_equal(gmx, pts.max(0))
+        vaxis, vcuts = sh.slab_cuts(part, world, 0.1, min_bound=gmn)
+        mine_v = sh.redistribute(part, vaxis, vcuts, rank, world, grid=(gmn, 0.1))
+        assert np.all(sh.slab_of(mine_v, vaxis, vcuts, (gmn, 0.1)) == rank)
+        loc = orc.voxel_trace(mine_v, 0.1, min_bound=gmn, max_bound=gmx)
+        rows = sh.gather_voxel_rows(dict(V=loc["V"], keys=loc["keys"].astype(np.int64), count=loc["count"], centroid=loc["centroid"]), rank, world)
+        ref = orc.voxel_trace(pts, 0.1)
+        assert rows["V_total"] == ref["V"] and np.array_equal(rows["keys"], ref["keys"]) and np.array_equal(rows["count"], ref["count"])
+        assert np.abs(rows["centroid"] - ref["centroid"]).max() <= 1e-12 * np.abs(ref["centroid"]).max()
         q.put((rank, "ok", [float(c) for c in cuts]))
     except Exception as ex:   # noqa: BLE001
         import traceback
