@@ -307,7 +307,7 @@ def run_c4(rank, world, local, dist, barrier, frames_total=256, points=131072):
     distinct = 8
     frames = {f: lidar_like(points, 2000 + f, np.float32) for f in range(distinct)}
     det = Processors.PlaneDetection(distance_threshold=THR, num_iterations=ITERS, alpha=1.0, seed=7)
-    pipes = [Processors.CPUNormals(), det, Processors.PlaneNormalize(detection_uuid=det.uuid)]
+    pipes = [Processors.CPUNormals(pinned_outputs=True), det, Processors.PlaneNormalize(detection_uuid=det.uuid, pinned_outputs=True)]
     mat = PointCloudMat(shape_type=ShapeType.XYZ).build(frames[0])
     PointCloudMatProcessors.run_once([mat], {}, pipes, validate=True)
     sec = 0.0
@@ -318,7 +318,7 @@ def run_c4(rank, world, local, dist, barrier, frames_total=256, points=131072):
             PointCloudMatProcessors.run_once([mat], {}, pipes)
         barrier(); sec = time.perf_counter() - t0
     sec = _max_over_ranks([sec], dist, local)[0]
-    return {"workload": f"C4: {frames_total} frames x {points} points through CPUNormals -> PlaneDetection -> PlaneNormalize (run_once), frame f -> rank f mod G, host float32 frames in, host arrays out",
+    return {"workload": f"C4: {frames_total} frames x {points} points through CPUNormals -> PlaneDetection -> PlaneNormalize (run_once), frame f -> rank f mod G, host float32 frames in, host arrays out (page-locked output buffers, two per block)",
             "frames": frames_total, "frames_per_s": frames_total / sec, "mpoints_per_s": frames_total * points / sec / 1e6,
             "ms_per_frame_per_gpu": 1e3 * sec / max(len(mine), 1), "collectives_on_data_path": 0}
 
@@ -340,9 +340,10 @@ def run_c5(ctx, nat, rank, world, local, dist, barrier, total):
     barrier(); t_red = time.perf_counter() - t0
     moved = int(len(part)) if world > 1 else 0          # upper bound of the rows this rank sends in the redistribution
     del part
-    barrier(); t0 = time.perf_counter()
-    vres = sh.slab_voxel_down_sample(ctx, owned, rank, world, VOXEL, axis, cuts, gmn, gmx, fields=("rep",))
-    barrier(); t_vox = time.perf_counter() - t0
+    for _ in range(2):                        # first call = warm-up (buffer growth)
+        barrier(); t0 = time.perf_counter()
+        vres = sh.slab_voxel_down_sample(ctx, owned, rank, world, VOXEL, axis, cuts, gmn, gmx, fields=("rep",), want_keys=False)
+        barrier(); t_vox = time.perf_counter() - t0
     out["cut_redistribute_ms"] = _max_over_ranks([t_red * 1e3], dist, local)[0]
     out["voxel"] = {"ms": _max_over_ranks([t_vox * 1e3], dist, local)[0], "voxels_total": vres["V_total"], "collectives": "all-reduce(min) of 6 doubles + all-gather of the row counts; no halo"}
     out["redistribution_bytes_upper_bound_per_rank"] = moved * 24

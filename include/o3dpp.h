@@ -120,6 +120,9 @@ O3DPP_API int o3dpp_bounds(o3dpp_ctx *ctx, double *min3, double *max3);
 /* ---- transform: replaces pcd.transform(T) (PointCloud.py:60-62) ------------------ */
 /* T = 16 float64 row-major.  points: (T[p,1]).xyz / w ; normals (if present): (T[n,0]).xyz */
 O3DPP_API int o3dpp_transform(o3dpp_ctx *ctx, const double *T16);
+/* points only, normals left as they are: PlaneNormalize.rotate_to_plane (processors.py:725-744) transforms pcd[:, :3]
+ * and passes every other column of the mat through unchanged, normal columns included */
+O3DPP_API int o3dpp_transform_points(o3dpp_ctx *ctx, const double *T16);
 
 /* ---- voxel_down_sample_and_trace: replaces pcd.voxel_down_sample_and_trace(
  *      voxel_size, min_bound, max_bound, approximate_class=False) (PointCloud.py:338-341)

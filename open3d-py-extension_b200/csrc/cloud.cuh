@@ -350,7 +350,7 @@ transform_kernel(double *__restrict__ x, double *__restrict__ y, double *__restr
     }
 }
 
-static int transform_impl(o3dpp_ctx *c, const double *T16)
+static int transform_impl(o3dpp_ctx *c, const double *T16, int what = 3)      // what: 1 = points, 2 = normals, 3 = both
 {
     if (!T16) return set_err(O3DPP_E_ARG, "null matrix");
     Mat4 T;
@@ -360,8 +360,8 @@ static int transform_impl(o3dpp_ctx *c, const double *T16)
     invalidate_derived(c);
     int grid = grid_for(c, (n + 1) / 2, 256, 8);
     cudaEventRecord(c->ev[0], c->stream);
-    LAUNCH(c, transform_kernel, grid, 256, 0, c->pts.x(), c->pts.y(), c->pts.z(), n, T, 0);
-    if (c->nrm.present)
+    if (what & 1) LAUNCH(c, transform_kernel, grid, 256, 0, c->pts.x(), c->pts.y(), c->pts.z(), n, T, 0);
+    if ((what & 2) && c->nrm.present)
         LAUNCH(c, transform_kernel, grid, 256, 0, c->nrm.x(), c->nrm.y(), c->nrm.z(), n, T, 1);
     cudaEventRecord(c->ev[1], c->stream);
     return check_launch("transform");

@@ -68,8 +68,11 @@ static int launch_lane(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, K
     O3_TRY(compact_indices(c, pred, n, list, &m2));
     if (m2 > 0) {
         auto k2 = knn_range_kernel<MODE>;
-        int64_t warps2 = (m2 + 31) / 32;
-        LAUNCH(c, k2, (int)((warps2 + K2_WARPS - 1) / K2_WARPS), K2_WARPS * 32, 0, gd, K, radius, out, list, (int)m2, capbuf);
+        // queries per warp: 32 when the failed queries fill the machine many times over, fewer (down to 2) when they do not
+        int qpw = (int)(m2 / ((int64_t)c->sm_count * 32));
+        qpw = qpw < 2 ? 2 : (qpw > 32 ? 32 : qpw);
+        int64_t warps2 = (m2 + qpw - 1) / qpw;
+        LAUNCH(c, k2, (int)((warps2 + K2_WARPS - 1) / K2_WARPS), K2_WARPS * 32, 0, gd, K, radius, out, list, (int)m2, capbuf, qpw);
         O3_TRY(check_launch("knn_range"));
         cudaEventRecord(c->ev[5], c->stream);
         O3_TRY(compact_indices(c, pred, n, list, &m3));

@@ -151,13 +151,15 @@ struct K2Range {
 template <int MODE>
 __global__ void __launch_bounds__(K2_WARPS * 32)
 knn_range_kernel(const GridDesc g, int K, double radius, KnnOut out, const int32_t *__restrict__ list, int m,
-                 float *__restrict__ capbuf)
+                 float *__restrict__ capbuf, int qpw)
 {
+    // qpw = queries per warp (<= 32): 32 amortises the warp's set-up when there are millions of failed queries; a frame-sized
+    // cloud leaves a few thousand, and fewer per warp then means more warps to fill the machine (the host picks it)
     __shared__ K2WarpMem k2_sm[K2_WARPS];
     const int lane = lane_id(), w = threadIdx.x >> 5;
-    const int64_t first = ((int64_t)blockIdx.x * K2_WARPS + w) * 32;
+    const int64_t first = ((int64_t)blockIdx.x * K2_WARPS + w) * qpw;
     if (first >= m) return;
-    const int nq = (int)(m - first < 32 ? m - first : 32);
+    const int nq = (int)(m - first < qpw ? m - first : qpw);
     K2WarpMem &sm = k2_sm[w];
     // lane i owns query i of the batch
     int myq = -1;

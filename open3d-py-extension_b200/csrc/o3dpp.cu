@@ -256,6 +256,14 @@ O3DPP_API int o3dpp_transform(o3dpp_ctx *c, const double *T16)
     return 0;
 }
 
+O3DPP_API int o3dpp_transform_points(o3dpp_ctx *c, const double *T16)
+{
+    CTX_CHECK(c);
+    O3_TRY(transform_impl(c, T16, 1));
+    CU_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
 O3DPP_API int o3dpp_voxel(o3dpp_ctx *c, double voxel_size, int64_t *V)
 {
     CTX_CHECK(c);

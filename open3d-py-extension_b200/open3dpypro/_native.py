@@ -33,7 +33,7 @@ SYMBOLS = [
     "o3dpp_select_inliers", "o3dpp_sample_philox", "o3dpp_planes_from_points", "o3dpp_score_planes",
     "o3dpp_plane_inliers", "o3dpp_inlier_moments", "o3dpp_fetch_kth_bound", "o3dpp_knn_mean_distance", "o3dpp_zsplat", "o3dpp_download_async",
     "o3dpp_set_option", "o3dpp_fetch_neighbors", "o3dpp_voxel_bounded", "o3dpp_download_as", "o3dpp_download_rows6",
-    "o3dpp_host_register", "o3dpp_host_unregister", "o3dpp_fp64_peak",
+    "o3dpp_host_register", "o3dpp_host_unregister", "o3dpp_fp64_peak", "o3dpp_transform_points",
 ]
 
 _lib = None
@@ -244,6 +244,12 @@ class Context:
         return mn, mx
 
     # ---- operations
+    def transform_points(self, T):
+        """points only; normals (if any) stay as they are"""
+        T = np.ascontiguousarray(np.asarray(T, dtype=np.float64).reshape(16))
+        self.generation += 1
+        _check(lib().o3dpp_transform_points(self._h, _ptr(T)))
+
     def transform(self, T):
         T = np.ascontiguousarray(np.asarray(T, dtype=np.float64).reshape(16))
         self.generation += 1

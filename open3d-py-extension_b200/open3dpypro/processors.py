@@ -44,10 +44,11 @@ def _xyz(pcd):
 class _OnDevice:
     """the device copy a block left behind: valid while the array object is the one handed on and nothing else has
     changed the points of that context (Context.generation)"""
-    __slots__ = ("ref", "ctx", "generation")
+    __slots__ = ("ref", "ctx", "generation", "normals_cols")
 
-    def __init__(self, arr, ctx):
+    def __init__(self, arr, ctx, normals_cols=False):
         self.ref, self.ctx, self.generation = weakref.ref(arr), ctx, ctx.generation
+        self.normals_cols = normals_cols      # the device normals are arr[:, 3:6] (arr has exactly six columns)
 
 
 def _require_array(pcd):
@@ -65,6 +66,19 @@ class _DeviceBlock(PointCloudMatProcessor):
     reference's blocks find the CUDA tensor NumpyToTorch made (reference processors.py:188-209, :651-663).  float32
     mats travel as float32 (12 B/point); CUDA tensor mats are read and written in place through the *_dev calls."""
     multi_gpu: int = -1
+    pinned_outputs: bool = False     # outputs land in two alternating page-locked buffers per mat (full-speed D2H); a result
+    _pinned: dict = {}               # is then valid until the block has run twice more, like a shm writer's segment
+
+    def _out(self, i, shape, dtype):
+        """host array for the output of mat i"""
+        if not self.pinned_outputs:
+            return np.empty(shape, dtype)
+        key = (i, tuple(shape), np.dtype(dtype).str)
+        ent = self._pinned.get(key)
+        if ent is None:
+            ent = self._pinned[key] = [[nat.PinnedArray(shape, dtype), nat.PinnedArray(shape, dtype)], 0]
+        ent[1] ^= 1
+        return ent[0][ent[1]].array
 
     def _device(self, i):
         """mat i -> cuda:{i % num_gpus} inside one process (reference :206); a process pinned to one GPU
@@ -83,12 +97,13 @@ class _DeviceBlock(PointCloudMatProcessor):
             return nat.context(pcd.device.index)
         return nat.context(self._device(i))
 
-    def _resident(self, i, pcd, meta):
-        """-> context of mat i whose points are pcd[:, :3] (uploaded unless the previous block left them there)"""
+    def _resident(self, i, pcd, meta, want_handle=False):
+        """-> context of mat i whose points are pcd[:, :3] (uploaded unless the previous block left them there);
+        want_handle: -> (context, the record the previous block left, or None after an upload)"""
         ctx = self._ctx(i, pcd)
         h = meta.get(_RES_KEY, {}).get(i) if isinstance(meta, dict) else None
         if h is not None and h.ref() is pcd and h.ctx is ctx and h.generation == ctx.generation and ctx.size() == len(pcd):
-            return ctx
+            return (ctx, h) if want_handle else ctx
         if _is_cuda_tensor(pcd):
             t = pcd[:, :3]
             if t.dtype not in (torch.float32, torch.float64):
@@ -99,13 +114,13 @@ class _DeviceBlock(PointCloudMatProcessor):
         else:
             ctx.upload(nat.ATTR_POINTS, _xyz(pcd))
         ctx.drop(nat.ATTR_NORMALS)
-        return ctx
+        return (ctx, None) if want_handle else ctx
 
     @staticmethod
-    def _leave(i, arr, ctx, meta):
-        """record that ctx now holds arr[:, :3] as its points"""
+    def _leave(i, arr, ctx, meta, normals_cols=False):
+        """record that ctx now holds arr[:, :3] as its points (normals_cols: and arr[:, 3:6] as its normals)"""
         if isinstance(meta, dict):
-            meta.setdefault(_RES_KEY, {})[i] = _OnDevice(arr, ctx)
+            meta.setdefault(_RES_KEY, {})[i] = _OnDevice(arr, ctx, normals_cols)
 
 
 class Processors:
@@ -150,13 +165,13 @@ class Processors:
                     out[:, :D] = pcd
                     out[:, D:] = nrm
                 else:                                         # = np.hstack([pcd, normals]) (float64) without the temporaries
-                    out = np.empty((len(pcd), D + 3), np.float64)
+                    out = self._out(i, (len(pcd), D + 3), np.float64)
                     if D == 3:
                         ctx.download_rows6(out)               # rows assembled on the device, one copy
                     else:
                         out[:, :D] = pcd
                         out[:, D:] = ctx.download(nat.ATTR_NORMALS)
-                self._leave(i, out, ctx, meta)
+                self._leave(i, out, ctx, meta, normals_cols=(D == 3))
                 res.append(out)
             return res
 
@@ -200,8 +215,8 @@ class Processors:
                 xyz = xyz[(self.z_lower < xyz[:, 2]) & (xyz[:, 2] < self.z_upper)]
                 ctx = self._resident(i, xyz, {})
             else:
-                ctx = self._resident(i, pcd, meta)
-                self._leave(i, pcd, ctx, meta)             # segment_plane leaves the points as they are
+                ctx, h = self._resident(i, pcd, meta, want_handle=True)
+                self._leave(i, pcd, ctx, meta, normals_cols=bool(h and h.normals_cols))    # segment_plane leaves the cloud as it is
             seed = self.seed if self.seed is not None else int(np.random.randint(0, 2**31 - 1))
             plane, _ = ctx.segment_plane(self.distance_threshold, 3, self.num_iterations,
                                          seed=seed + self._calls, fetch_inliers=False)
@@ -266,9 +281,19 @@ class Processors:
                 if dt not in (np.float32, np.float64):
                     dt = np.dtype(np.float64)
                 T = self.plane_to_T(models[i], dt)
-                ctx = self._resident(i, pcd, meta)
+                ctx, h = self._resident(i, pcd, meta, want_handle=True)
+                # T holds the mat-dtype values; the product runs in FP64 and is rounded once
+                rows6 = not cuda and h is not None and h.normals_cols and pcd.shape[1] == 6 and ctx.has(nat.ATTR_NORMALS)
+                if rows6:            # the other three columns are the normals the device still holds: rows assembled there, one copy
+                    ctx.transform_points(T.astype(np.float64))
+                    out = self._out(i, pcd.shape, dt)
+                    ctx.download_rows6(out)
+                    self._leave(i, out, ctx, meta, normals_cols=True)
+                    res.append(out)
+                    self.forward_T[i] = T.tolist()
+                    continue
                 ctx.drop(nat.ATTR_NORMALS)
-                ctx.transform(T.astype(np.float64))      # T holds the mat-dtype values; the product runs in FP64 and is rounded once
+                ctx.transform(T.astype(np.float64))
                 if cuda:
                     out = torch.empty_like(pcd)
                     xyz = out if pcd.shape[1] == 3 else torch.empty((len(pcd), 3), dtype=pcd.dtype, device=pcd.device)
@@ -277,7 +302,7 @@ class Processors:
                         out[:, :3] = xyz
                         out[:, 3:] = pcd[:, 3:]
                 else:
-                    out = np.empty(pcd.shape, dt)              # = np.hstack([xyz, pcd[:, 3:]]) in the mat's dtype
+                    out = self._out(i, pcd.shape, dt)          # = np.hstack([xyz, pcd[:, 3:]]) in the mat's dtype
                     if pcd.shape[1] == 3:
                         ctx.download_as(nat.ATTR_POINTS, out)
                     else:

@@ -393,7 +393,7 @@ def global_bounds(points, world: int, group=None) -> Tuple[np.ndarray, np.ndarra
 
 
 def slab_voxel_down_sample(ctx, owned, rank: int, world: int, voxel_size: float, axis: int, cuts, min_bound, max_bound,
-                           group=None, fields=("rep", "count", "centroid")):
+                           group=None, fields=("rep", "count", "centroid"), want_keys=True):
     """voxel_down_sample_and_trace of a scan sharded by slab (reference call: PointCloud.py:338-341, which passes the
     scan's min/max bound explicitly): every rank runs o3dpp_voxel_bounded on its own points with the GLOBAL bounds, so its
     voxel keys are the whole scan's.  The cuts lie on voxel planes and ownership is by voxel index (redistribute(grid=)),
@@ -419,9 +419,11 @@ def slab_voxel_down_sample(ctx, owned, rank: int, world: int, voxel_size: float,
     want = tuple(dict.fromkeys(tuple(fields) + ("rep",)))
     res = ctx.voxel_fetch(V, n, list(want)) if n else {k: np.empty((0,) + ((3,) if k == "centroid" else ()), np.float64 if k == "centroid" else np.int32) for k in want}
     rep = res["rep"]
-    rp = owned[torch.as_tensor(rep, device=owned.device).long()].double().cpu().numpy() if hasattr(owned, "is_cuda") else np.asarray(owned, dtype=np.float64)[rep]
-    keys = np.floor((rp - mn) / float(voxel_size)).astype(np.int64)           # FP64 subtract, divide, floor: the device's expression
-    if V:
+    keys = None
+    if want_keys:
+        rp = owned[torch.as_tensor(rep, device=owned.device).long()].double().cpu().numpy() if hasattr(owned, "is_cuda") else np.asarray(owned, dtype=np.float64)[rep]
+        keys = np.floor((rp - mn) / float(voxel_size)).astype(np.int64)           # FP64 subtract, divide, floor: the device's expression
+    if V and want_keys:
         k = cut_voxel_indices(cuts, axis, mn, voxel_size)
         lo = k[rank - 1] if rank > 0 else np.iinfo(np.int64).min
         hi = k[rank] if rank < world - 1 else np.iinfo(np.int64).max

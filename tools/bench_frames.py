@@ -33,7 +33,7 @@ from open3dpypro.synthetic import lidar_like
 mine = sh.frames_of_rank(a.frames, rank, world)
 frames = {f: lidar_like(a.points, 2000 + f) for f in range(min(a.distinct, a.frames))}      # float32 (N,3)
 det = Processors.PlaneDetection(distance_threshold=0.05, num_iterations=1000, alpha=1.0, seed=7)
-pipes = [Processors.CPUNormals(), det, Processors.PlaneNormalize(detection_uuid=det.uuid)]      # O3DPP_DEVICE pins this rank's GPU
+pipes = [Processors.CPUNormals(pinned_outputs=True), det, Processors.PlaneNormalize(detection_uuid=det.uuid, pinned_outputs=True)]      # O3DPP_DEVICE pins this rank's GPU
 mat = PointCloudMat(shape_type=ShapeType.XYZ).build(frames[0])
 PointCloudMatProcessors.run_once([mat], {}, pipes, validate=True)
 
