@@ -113,82 +113,13 @@ __device__ __forceinline__ float kf_err(float t, float eA, float eC)
 // capbuf[q] < 0: answered by the selection kernel, |capbuf| bounds the k-th d2.  A query whose covariance is
 // order-sensitive (kf_store_normal's guard) is handed back (capbuf > 0) to the exact tier.
 //
-// The kernel is bound by the L1 wavefronts of the gather (every neighbour is a different 32-byte record of sp4; a
-// divergent 16-byte load costs one wavefront per lane), not by HBM or issue slots.  So a PAIR of lanes fetches one record
-// in ONE instruction (lane 2i the (x, y) half, lane 2i+1 the (z, -) half: 16 wavefronts for 16 neighbours instead of
-// 2 x 32 for 32), the halves are exchanged by shuffles, the even lane sums {x, y, xx, xy, yy}, the odd lane {z, xz, yz, zz}.
-// A warp takes its 32 queries in two rounds of 16; the totals are then dealt out one query per lane for the eigen-solve.
-#ifndef KC_PAIR
-#define KC_PAIR 0       // measured at 10 M: lane pairs 2.16 ms, thread per query 1.58 ms (the kernel is latency bound, not L1-wavefront bound)
-#endif
+// Thread per query, the K gathers in batches of KC_UNR.  Measured at 10 M and not kept: a lane PAIR per 32-byte record (16 + 16
+// bytes in one instruction, to halve the L1 wavefronts) 2.16 ms against 1.58 (the kernel is latency bound, not wavefront bound);
+// running it on a second stream beside tiers 2 and 3 (it fills the register file: the kernels serialise anyway).
+// 64 registers (KC_MINB 8) against 88: 1.30 against 1.58 ms.
 #ifndef KC_MINB
 #define KC_MINB 8       // resident 128-thread blocks per SM the register budget is set for
 #endif
-#if KC_PAIR
-template <int MODE>
-__global__ void __launch_bounds__(128)
-knn_finish_kernel(const GridDesc g, int K, double radius, KnnOut out, float *__restrict__ capbuf)
-{
-    const int lane = lane_id();
-    const int64_t q0 = ((int64_t)blockIdx.x * 4 + (threadIdx.x >> 5)) * 32;      // the warp's 32 queries (sorted positions)
-    if (q0 >= g.n) return;
-    const int64_t myq = q0 + lane;
-    const float mycap = myq < g.n ? capbuf[myq] : 0.0f;
-    if (!__any_sync(FULL, mycap < 0.0f)) return;
-    const double r2 = __dmul_rn(radius, radius);
-    const int half = lane & 1;
-    Cumul mine;
-    mine.clear();
-    for (int r = 0; r < 2; ++r) {
-        const int64_t q = q0 + r * 16 + (lane >> 1);                     // the pair's query of this round
-        const bool live = q < g.n && __shfl_sync(FULL, mycap, r * 16 + (lane >> 1)) < 0.0f;
-        // own query (hybrid: the FP64 radius test needs it): even lane (x, y), odd lane (z, -)
-        double qa = 0, qb = 0;
-        if (MODE == 2 && live) { const double2 t = ((const double2 *)(g.sp4 + q))[half]; qa = t.x; qb = t.y; }
-        const double qz = shfl_xor_d(qa, 1), qx = shfl_xor_d(qa, 1), qy = shfl_xor_d(qb, 1);    // odd: (qx, qy) of the even lane; even: qz
-        double s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0;     // even: x y xx xy yy ; odd: z xz yz zz (s4 unused)
-        int cnt = 0;
-        const uint32_t *nb = out.nbr + (live ? q : q0);
-        for (int j0 = 0; j0 < K; j0 += KC_UNR) {
-            uint32_t p[KC_UNR];
-            double2 v[KC_UNR];
-#pragma unroll
-            for (int u = 0; u < KC_UNR; ++u) p[u] = (live && j0 + u < K) ? nb[(int64_t)(j0 + u) * out.nbr_pitch] : KNN_NONE;
-#pragma unroll
-            for (int u = 0; u < KC_UNR; ++u) v[u] = ((const double2 *)(g.sp4 + (p[u] != KNN_NONE ? (int64_t)p[u] : q0)))[half];
-#pragma unroll
-            for (int u = 0; u < KC_UNR; ++u) {
-                // the partner's half: even receives (z, -), odd receives (x, y)
-                const double oa = shfl_xor_d(v[u].x, 1), ob = shfl_xor_d(v[u].y, 1);
-                const double x = half ? oa : v[u].x, y = half ? ob : v[u].y, z = half ? v[u].x : oa;
-                bool take = p[u] != KNN_NONE;
-                if (MODE == 2) {
-                    const double ax = half ? qx : qa, ay = half ? qy : qb, az = half ? qa : qz;
-                    take = take && dist2_rn(ax, ay, az, x, y, z) < r2;
-                }
-                if (take) {
-                    if (!half) { s0 += x; s1 += y; s2 += x * x; s3 += x * y; s4 += y * y; }
-                    else       { s0 += z; s1 += x * z; s2 += y * z; s3 += z * z; }
-                    cnt++;
-                }
-            }
-        }
-        // deal the totals out: lane i of the warp finishes query i; its sums sit in lanes 2 (i & 15), 2 (i & 15) + 1 of round i >> 4
-        const int src = 2 * (lane & 15);
-        const double e0 = shfl_d(s0, src), e1 = shfl_d(s1, src), e2 = shfl_d(s2, src), e3 = shfl_d(s3, src), e4 = shfl_d(s4, src);
-        const double o0 = shfl_d(s0, src + 1), o1 = shfl_d(s1, src + 1), o2 = shfl_d(s2, src + 1), o3 = shfl_d(s3, src + 1);
-        const int n = __shfl_sync(FULL, cnt, src);
-        if ((lane >> 4) == r) {
-            mine.c[0] = e0; mine.c[1] = e1; mine.c[2] = o0;
-            mine.c[3] = e2; mine.c[4] = e3; mine.c[5] = o1;
-            mine.c[6] = e4; mine.c[7] = o2; mine.c[8] = o3;
-            mine.n = n;
-        }
-    }
-    if (!(mycap < 0.0f)) return;
-    if (!kf_store_normal(mine, g.sidx[myq], out, KL_GUARD)) capbuf[myq] = -mycap;
-}
-#else
 template <int MODE>
 __global__ void __launch_bounds__(128, KC_MINB)
 knn_finish_kernel(const GridDesc g, int K, double radius, KnnOut out, float *__restrict__ capbuf)
@@ -216,7 +147,6 @@ knn_finish_kernel(const GridDesc g, int K, double radius, KnnOut out, float *__r
     }
     if (!kf_store_normal(cu, g.sidx[q], out, KL_GUARD)) capbuf[q] = -cap;
 }
-#endif
 
 // ---- recorded neighbour sets -> sorted original indices ------------------------------------------------------------
 __global__ void __launch_bounds__(256)

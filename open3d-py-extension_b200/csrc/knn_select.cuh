@@ -57,6 +57,9 @@
 #ifndef KS_WIN
 #define KS_WIN 2        // unstageable groups: cell groups taken before and after the home group along the curve
 #endif
+#ifndef KS_LANE_RHO
+#define KS_LANE_RHO 1   // certify completeness against rho + the query's own clearance inside the home box instead of rho
+#endif
 #ifndef KS_MINB
 #define KS_MINB (KS_W == 2 ? 10 : 11)    // resident blocks per SM the register budget is set for
 #endif
@@ -102,8 +105,7 @@ __device__ __forceinline__ void kl_sts32(unsigned a, float v) { asm volatile("st
 // bin of a non-negative float relative to `base`: monotone in d2, three integer instructions; KS_NB = beyond the range
 __device__ __forceinline__ int kl_bin(float d, int base)
 {
-    int b = (__float_as_int(d) >> KS_SHIFT) - base;
-    return min(max(b, 0), KS_NB);
+    return __vimin_s32_relu((__float_as_int(d) >> KS_SHIFT) - base, KS_NB);      // max(min(b, KS_NB), 0) in one instruction
 }
 
 // lower bound of the squared gap between the home box (flo, fhi: rounded outwards) and box c of table lvl, in FP32 with
@@ -387,7 +389,17 @@ knn_select_kernel(const GridDesc g, int K, double radius, float rho_scale, int m
     // error model of the staged FP32 coordinates: |coordinate| <= half home extent + rho (window: the largest staged)
     const float Lf = (float)((window ? fmax(0.5 * h.hext, wmax) : 0.5 * h.hext + rho) * 1.001);
     const float eA = 16.0f * KF_U * Lf, eC = 2.3e-13f * Lf * Lf;
-    const float rho1f = staged ? __double2float_rd(rho * rho * (1.0 - 1e-6)) : -1.0f;
+    // completeness radius of THIS lane: every point within rho of the home box is staged (its group's box is within rho of the
+    // home box, so the group is listed, and the point lies inside the grown box), and the ball of radius delta = the query's
+    // distance to the nearest face of the home box lies inside the home box: everything within rho + delta of the query is staged
+    double delta = 0.0;
+    if (valid) delta = fmin(fmin(fmin(px - h.lo[0], h.hi[0] - px), fmin(py - h.lo[1], h.hi[1] - py)), fmin(pz - h.lo[2], h.hi[2] - pz));
+#if KS_LANE_RHO
+    const double rlane = rho + fmax(delta, 0.0) * (1.0 - 1e-9);
+#else
+    const double rlane = rho;
+#endif
+    const float rho1f = staged ? __double2float_rd(rlane * rlane * (1.0 - 1e-6)) : -1.0f;
     float tcap = KF_TCAP;
     bool select = nq >= K && have;
     if (MODE == 2) {
