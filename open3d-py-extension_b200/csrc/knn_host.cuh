@@ -31,11 +31,12 @@ static int launch_lane(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, K
         out.tier = c->g_tier.as<unsigned char>();
         CU_TRY(cudaMemsetAsync(out.tier, 0, (size_t)n, c->stream));
     }
-    // rho = staging radius / home-box diagonal (0.44: measured optimum on the LiDAR-like scans).  A list longer than gsplit,
+    // rho = staging radius / home-box diagonal (0.42: measured optimum on the LiDAR-like scans, all tiers, 10 M: 0.44 -> 11.43 ms,
+    // 0.42 -> 11.30, 0.40 -> 11.4).  A list longer than gsplit,
     // or candidates that overflow the staging area, retry with the radius x shrink, up to max_shrink times
     // (gsplit at 10M, all three tiers: 48 -> 13.40 ms, 64 -> 13.23, 80 -> 13.30, 96 -> 13.42, 128 -> 13.47)
     const KnnTune &t = c->tune;
-    const float rho = t.rho > 0.f ? t.rho : 0.44f;
+    const float rho = t.rho > 0.f ? t.rho : 0.42f;
     const int max_shrink = t.max_shrink >= 0 && t.max_shrink <= 12 ? t.max_shrink : 12;
     const int gsplit = t.gsplit >= 16 && t.gsplit <= KS_GMAX - 64 ? t.gsplit : 64;
     const float shrink = t.shrink > 0.1f && t.shrink < 0.99f ? t.shrink : 0.7f;

@@ -67,7 +67,7 @@
 #define KA_WARPS 8
 #endif
 #ifndef KS_LIST
-#define KS_LIST 56      // survivors of the threshold pass per query (16-bit staged slots): < K + KS_BND
+#define KS_LIST 55      // survivors of the threshold pass per query (16-bit staged slots): >= K - 1 + KS_BND + 1; 55 keeps the block at 20 064 B = 11 groups per SM
 #endif
 #define KS_NOLIST 0xffffu
 
@@ -239,8 +239,10 @@ struct KsMem {
         unsigned short nb[KS_LIST * 32];                                          // [j][lane] staged slots: survivors, then the neighbours; two-ended
         unsigned gl[KS_GMAX];                                                     // cell groups to scan (staging only)
     } v;
-    unsigned short na[2][32], nbd[2][32];     // pass C, per warp and lane: neighbours / boundary entries collected
+#if KS_W > 1                                  // what the two warps tell each other (one warp: registers; 20.1 KB per group = 11 groups per SM)
+    unsigned short na[2][32], nbd[2][32];     // pass F, per warp and lane: neighbours / boundary entries collected
     unsigned char ok[32], cn_up[32], cn_dn[32];
+#endif
     int n_lo, n_hi, ng;
     double wmax;
 };
@@ -491,12 +493,19 @@ knn_select_kernel(const GridDesc g, int K, double radius, float rho_scale, int m
                 if (b < bstar) { kl_sts16(nba, (unsigned short)sl); nba += stn; }
                 else if (b == beq) { kl_sts32(bda, d); kl_sts16(bsa, (unsigned short)sl); bda += std_; bsa += stn; }
             }
-            sm.na[w][lane] = (unsigned short)((int)(nba - la0) / stn);
-            sm.nbd[w][lane] = (unsigned short)((int)(bsa - bs0) / stn);
         }
+        const int mya = (int)(nba - la0) / stn, myb = (int)(bsa - bs0) / stn;
+#if KS_W > 1
+        sm.na[w][lane] = (unsigned short)mya;
+        sm.nbd[w][lane] = (unsigned short)myb;
+#endif
         ks_sync<W>();
         if (w == 0) {
-            const int a0 = sm.na[0][lane], a1 = W > 1 ? sm.na[1][lane] : 0, b0 = sm.nbd[0][lane], b1 = W > 1 ? sm.nbd[1][lane] : 0;
+#if KS_W > 1
+            const int a0 = sm.na[0][lane], a1 = sm.na[1][lane], b0 = sm.nbd[0][lane], b1 = sm.nbd[1][lane];
+#else
+            const int a0 = mya, a1 = 0, b0 = myb, b1 = 0;
+#endif
             float *bd = sm.u.bnd.d + lane;               // warp 0's entries at [0, b0), warp 1's at [KS_BND - b1, KS_BND)
             const unsigned short *bs = sm.u.bnd.s + lane;
             const float ubound = U + kf_err(U, eA, eC) * 1.0001f;
@@ -537,10 +546,14 @@ knn_select_kernel(const GridDesc g, int K, double radius, float rho_scale, int m
                 if (!c1) why = 1; else if (!c2) why = 2;
             }
             if (window) { ok = false; why = 5; }      // rho1f < 0 already refuses; the bound capf is what counts
+#if KS_W > 1
             sm.ok[lane] = ok ? 1 : 0; sm.cn_up[lane] = (unsigned char)cn_up; sm.cn_dn[lane] = (unsigned char)cn_dn;
+#endif
         }
         ks_sync<W>();
-        if (W > 1) { ok = sm.ok[lane] != 0; cn_up = sm.cn_up[lane]; cn_dn = sm.cn_dn[lane]; }
+#if KS_W > 1
+        ok = sm.ok[lane] != 0; cn_up = sm.cn_up[lane]; cn_dn = sm.cn_dn[lane];
+#endif
     } else if (nq >= K) {
         capf = U + kf_err(U, eA, eC) * 1.0001f;
     }
