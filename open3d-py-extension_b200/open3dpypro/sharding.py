@@ -198,10 +198,11 @@ def slab_estimate_normals(ctx, owned: np.ndarray, axis: int, cuts: Sequence[floa
     """estimate_normals of the points this rank owns, equal to the single-GPU result on the whole scan.
 
     hybrid / radius search: one halo exchange of width `radius` (exact).  Pure KNN: a first pass over the
-    owned points alone bounds every query's k-th distance (o3dpp_fetch_kth_bound); the halo width is the
-    largest bound among the queries that could reach across a cut (all-reduce MAX), then one exchange and
-    the final pass.  Returns (normals of the owned points, info dict).  The context is left holding
-    owned + halo points (owned first)."""
+    owned points alone answers every query whose k-th distance bound (o3dpp_fetch_kth_bound) stays short of
+    the cut; the halo width is the largest bound among the others (all-reduce MAX), one exchange, and a
+    second pass over just the strips along the cuts (own points within two halo widths + the halo) for those
+    queries.  Returns (normals of the owned points, info dict).  The context is left holding the owned points
+    first (hybrid / radius: followed by the halo)."""
     from . import _native as nat
     owned = np.ascontiguousarray(owned, dtype=np.float64).reshape(-1, 3)
     n_own = len(owned)
@@ -212,21 +213,42 @@ def slab_estimate_normals(ctx, owned: np.ndarray, axis: int, cuts: Sequence[floa
         ctx.estimate_normals(mode, knn, radius)
         return _download_normals(ctx, n_own), info
     if mode == nat.SEARCH_KNN:
+        # pass 1: the owned points alone.  A query whose k-th distance bound r stays short of the cut already has its global
+        # neighbours (safe); the others need the points of the neighbour slabs within r of the cut
         ctx.upload(nat.ATTR_POINTS, owned)
         ctx.drop(nat.ATTR_NORMALS)
         h_need = 0.0
+        unsafe = np.zeros(n_own, bool)
+        nrm = np.empty((0, 3))
         if n_own:
             ctx.estimate_normals(mode, knn, radius)
+            nrm = _download_normals(ctx, n_own)
             r = np.sqrt(ctx.kth_bound().astype(np.float64)) * (1.0 + 1e-6)
             x = owned[:, axis]
             to_cut = np.minimum(x - cuts[rank], cuts[rank + 1] - x)        # +-inf at the outer faces
             unsafe = r > to_cut
             if unsafe.any():
                 h_need = float(r[unsafe].max())
-            info["passes"] = 2
         halo_w = float(_allreduce(np.array([h_need]), "max", group)[0])
-        if not np.isfinite(halo_w):                                          # a slab with fewer than k points
-            halo_w = float(_allreduce(np.array([np.ptp(owned[:, axis]) if n_own else 0.0]), "sum", group)[0]) + 1.0
+        if np.isfinite(halo_w):
+            # pass 2, only for the unsafe queries: they lie within halo_w of a cut and their balls reach at most 2 halo_w into
+            # the own slab and halo_w into the neighbours', so a cloud of just those strips holds all their global neighbours
+            halo = exchange_halo(owned, axis, cuts, rank, world, halo_w, group)
+            info.update(halo_width=halo_w, halo_points=int(len(halo)), passes=2)
+            if unsafe.any():
+                near = to_cut <= 2.0 * halo_w
+                ctx.upload(nat.ATTR_POINTS, np.concatenate([owned[near], halo], 0))
+                ctx.drop(nat.ATTR_NORMALS)
+                ctx.estimate_normals(mode, knn, radius)
+                n2 = _download_normals(ctx, int(near.sum()))
+                nrm[unsafe] = n2[(np.cumsum(near) - 1)[unsafe]]
+                info["second_pass_points"] = int(near.sum()) + int(len(halo))
+            ctx.upload(nat.ATTR_POINTS, owned)          # the context is left holding the owned points (slab_segment_plane)
+            ctx.drop(nat.ATTR_NORMALS)
+            return nrm, info
+        # a slab with fewer than k points: no bound at all; one pass over everything with a halo as wide as the scan
+        halo_w = float(_allreduce(np.array([np.ptp(owned[:, axis]) if n_own else 0.0]), "sum", group)[0]) + 1.0
+        info["passes"] = 2
     else:
         halo_w = float(radius)
     halo = exchange_halo(owned, axis, cuts, rank, world, halo_w, group)
@@ -558,7 +580,7 @@ def dev_exchange_halo(owned, axis: int, cuts, rank: int, world: int, halo: float
 def dev_slab_estimate_normals(ctx, owned, axis: int, cuts, rank: int, world: int, mode: int, knn: int, radius: float = 0.0,
                               group=None):
     """slab_estimate_normals on device tensors: -> (normals of the owned points as a CUDA tensor, info).
-    The context is left holding owned + halo points (owned first)."""
+    The context is left holding the owned points first (hybrid / radius: followed by the halo)."""
     import torch
     from . import _native as nat
     n_own = len(owned)
@@ -573,36 +595,63 @@ def dev_slab_estimate_normals(ctx, owned, axis: int, cuts, rank: int, world: int
             ctx.estimate_normals(mode, knn, radius)
         return loc
 
+    import time
+
+    def fetch(n_keep):
+        out = torch.empty((ctx.size(), 3), dtype=torch.float64, device=owned.device)
+        if len(out):
+            ctx.download_dev(nat.ATTR_NORMALS, out.data_ptr(), nat.F64)
+            ctx.synchronize()
+        return out[:n_keep]
+
+    def exchange(width):
+        _sync_torch()
+        t0 = time.perf_counter()
+        halo = dev_exchange_halo(owned, axis, cuts, rank, world, width, group)
+        _sync_torch()
+        info.update(halo_width=width, halo_points=int(len(halo)), halo_bytes=int(len(halo)) * 24,
+                    exchange_ms=(time.perf_counter() - t0) * 1e3)
+        return halo
+
     if world > 1 and mode == nat.SEARCH_KNN:
+        # the same two passes as slab_estimate_normals: all owned points alone, then only the strips along the cuts for the
+        # queries whose k-th distance bound reaches across a cut
         h_need = 0.0
+        unsafe = None
+        nrm = owned[:0]
         if n_own:
             run(owned)
+            nrm = fetch(n_own)
             r = torch.from_numpy(ctx.kth_bound()).to(owned.device).double().sqrt_() * (1.0 + 1e-6)
             x = owned[:, axis]
             to_cut = torch.minimum(x - float(cuts[rank]), float(cuts[rank + 1]) - x)
             unsafe = r > to_cut
             if bool(unsafe.any()):
                 h_need = float(r[unsafe].max())
-            info["passes"] = 2
         halo_w = float(_allreduce(np.array([h_need]), "max", group)[0])
-        if not np.isfinite(halo_w):
-            span = float(owned[:, axis].max() - owned[:, axis].min()) if n_own else 0.0
-            halo_w = float(_allreduce(np.array([span]), "sum", group)[0]) + 1.0
+        if np.isfinite(halo_w):
+            halo = exchange(halo_w)
+            info["passes"] = 2
+            if unsafe is not None and bool(unsafe.any()):
+                near = to_cut <= 2.0 * halo_w
+                n_near = int(near.sum())
+                run(torch.cat([owned[near], halo], 0))
+                n2 = fetch(n_near)
+                nrm[unsafe] = n2[(torch.cumsum(near.long(), 0) - 1)[unsafe]]
+                info["second_pass_points"] = n_near + int(len(halo))
+            if n_own:
+                _sync_torch()
+                ctx.upload_dev(nat.ATTR_POINTS, owned.contiguous().data_ptr(), n_own, nat.F64)   # left holding the owned points
+                ctx.drop(nat.ATTR_NORMALS)
+            return nrm, info
+        span = float(owned[:, axis].max() - owned[:, axis].min()) if n_own else 0.0
+        halo_w = float(_allreduce(np.array([span]), "sum", group)[0]) + 1.0
+        info["passes"] = 2
     else:
         halo_w = float(radius) if world > 1 else 0.0
-    import time
-    _sync_torch()
-    t0 = time.perf_counter()
-    halo = dev_exchange_halo(owned, axis, cuts, rank, world, halo_w, group)
-    _sync_torch()
-    info.update(halo_width=halo_w, halo_points=int(len(halo)), halo_bytes=int(len(halo)) * 24,
-                exchange_ms=(time.perf_counter() - t0) * 1e3)
+    halo = exchange(halo_w)
     loc = run(torch.cat([owned, halo], 0) if len(halo) else owned)
-    out = torch.empty((len(loc), 3), dtype=torch.float64, device=owned.device)
-    if len(loc):
-        ctx.download_dev(nat.ATTR_NORMALS, out.data_ptr(), nat.F64)
-        ctx.synchronize()
-    return out[:n_own], info
+    return fetch(n_own), info
 
 
 def dev_slab_segment_plane(ctx, owned, rank: int, world: int, distance_threshold: float, ransac_n: int,
