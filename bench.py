@@ -333,6 +333,9 @@ def run_c5(ctx, nat, rank, world, local, dist, barrier, total):
     part = torch.from_numpy(lidar_like(total // world, SEED_C5 + rank, np.float32)).cuda(local).double()
     out = {"workload": f"C5: {total}-point scan sharded by spatial slab across {world} GPU(s): voxel_down_sample(0.1) + estimate_normals + segment_plane(0.05,3,1000)",
            "points": total}
+    if world > 1:                             # NCCL sets its peer connections up on first use (seconds at 8 ranks): not part of the scan
+        sh.dev_redistribute(part[:1024 * world].contiguous(), 0, np.concatenate([[-np.inf], np.linspace(-50, 50, world - 1), [np.inf]]), rank, world)
+        sh.global_bounds(part[:16], world)
     barrier(); t0 = time.perf_counter()
     gmn, gmx = sh.global_bounds(part, world)
     axis, cuts = sh.dev_slab_cuts(part, world, VOXEL, min_bound=gmn)
