@@ -616,7 +616,10 @@ def main():
             "roofline": {"bound": "hbm", "kernel": "knn_select_kernel (dominant) + knn_groups_kernel + knn_finish_kernel + knn_range_kernel + knn_exact_kernel: the whole "
                                                         "neighbour search of one estimate_normals call, every tier and the finish included in kernel_ms", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": ALGO_BYTES_PER_POINT_KNN * N, "kernel_ms": knn_ms},
+                         "algorithmic_bytes_per_launch": ALGO_BYTES_PER_POINT_KNN * N, "kernel_ms": knn_ms,
+                         "headline_formula": {"bytes": (384 + 12 + 12) * N + 16 * n_inl, "ms": t_metric,
+                                              "frac": ((384 + 12 + 12) * N + 16 * n_inl) / (t_metric * 1e-3) / 1e9 / peak,
+                                              "note": "BASELINE.md section 4: ((384+12+12) N + 16 I) / (t_normals + t_segment), grid build included"}},
             "clocks": clocks,
         }
         out.update(extras)

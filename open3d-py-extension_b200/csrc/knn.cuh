@@ -75,7 +75,7 @@ __device__ __forceinline__ uint64_t hilbert3(uint32_t x, uint32_t y, uint32_t z,
 
 __global__ void __launch_bounds__(256)
 curve_key_kernel(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
-                  int64_t n, const double *__restrict__ mnmx, int bits, uint64_t *__restrict__ keys)
+                  int64_t n, const double *__restrict__ mnmx, int bits, uint64_t *__restrict__ keys, double4 *__restrict__ p4)
 {
     double m0 = mnmx[0], m1 = mnmx[1], m2 = mnmx[2];
     double ext = fmax(fmax(mnmx[3] - m0, mnmx[4] - m1), mnmx[5] - m2);
@@ -91,19 +91,18 @@ curve_key_kernel(const double *__restrict__ x, const double *__restrict__ y, con
         if (cy > cmax) cy = cmax;
         if (cz > cmax) cz = cmax;
         keys[i] = hilbert3(cx, cy, cz, bits);
+        p4[i] = make_double4(x[i], y[i], z[i], 0.0);     // one 32-byte record per point: the gather below reads one sector, not three
     }
 }
 
 __global__ void __launch_bounds__(256)
-gather_sorted_kernel(const uint32_t *__restrict__ sidx, int64_t n, const double *__restrict__ x,
-                     const double *__restrict__ y, const double *__restrict__ z, double *__restrict__ sx,
+gather_sorted_kernel(const uint32_t *__restrict__ sidx, int64_t n, const double4 *__restrict__ p4, double *__restrict__ sx,
                      double *__restrict__ sy, double *__restrict__ sz, double4 *__restrict__ sp4)
 {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        uint32_t j = sidx[i];
-        double a = x[j], b = y[j], c = z[j];
-        sx[i] = a; sy[i] = b; sz[i] = c;
-        sp4[i] = make_double4(a, b, c, 0.0);
+        const double4 q = p4[sidx[i]];
+        sx[i] = q.x; sy[i] = q.y; sz[i] = q.z;
+        sp4[i] = make_double4(q.x, q.y, q.z, 0.0);
     }
 }
 
@@ -622,14 +621,15 @@ static int grid_build(o3dpp_ctx *c, GridDesc *gd)
     O3_TRY(c->g_sx.ensure(nn * 8)); O3_TRY(c->g_sy.ensure(nn * 8)); O3_TRY(c->g_sz.ensure(nn * 8));
     O3_TRY(c->g_sidx.ensure(nn * 4));
     O3_TRY(c->g_sp4.ensure(nn * 32));
+    O3_TRY(c->g_p4.ensure(nn * 32));
     int grid = grid_for(c, n, 256, 16);
     LAUNCH(c, curve_key_kernel, grid, 256, 0, c->pts.x(), c->pts.y(), c->pts.z(), n, c->d_small.as<double>(), bits,
-           c->s_keys0.as<uint64_t>());
+           c->s_keys0.as<uint64_t>(), c->g_p4.as<double4>());
     uint64_t *ks; uint32_t *vs;
     O3_TRY(radix_sort_pairs(c, c->s_keys0.as<uint64_t>(), c->s_keys1.as<uint64_t>(), c->s_vals0.as<uint32_t>(),
                             c->s_vals1.as<uint32_t>(), n, 3 * bits, &ks, &vs));
     CU_TRY(cudaMemcpyAsync(c->g_sidx.p, vs, (size_t)n * 4, cudaMemcpyDeviceToDevice, c->stream));
-    LAUNCH(c, gather_sorted_kernel, grid, 256, 0, c->g_sidx.as<uint32_t>(), n, c->pts.x(), c->pts.y(), c->pts.z(),
+    LAUNCH(c, gather_sorted_kernel, grid, 256, 0, c->g_sidx.as<uint32_t>(), n, c->g_p4.as<double4>(),
            c->g_sx.as<double>(), c->g_sy.as<double>(), c->g_sz.as<double>(), c->g_sp4.as<double4>());
     // range tables
     int L = 0;

@@ -18,7 +18,7 @@ struct VoxOrigin {                   // grid origin (min_bound) and the smallest
 __global__ void __launch_bounds__(256)
 voxel_key_kernel(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
                  int64_t n, const VoxOrigin og, double voxel_size, VoxPack pk, int wide,
-                 uint64_t *__restrict__ key_lo, uint32_t *__restrict__ key_ix, uint8_t *__restrict__ oct)
+                 uint64_t *__restrict__ key_lo, uint32_t *__restrict__ key_ix, double4 *__restrict__ p4)
 {
     const double m0 = og.o[0], m1 = og.o[1], m2 = og.o[2];
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -30,7 +30,7 @@ voxel_key_kernel(const double *__restrict__ x, const double *__restrict__ y, con
         if (__dsub_rn(r0, f0) >= 0.5) o |= 1;
         if (__dsub_rn(r1, f1) >= 0.5) o |= 2;
         if (__dsub_rn(r2, f2) >= 0.5) o |= 4;
-        oct[i] = (uint8_t)o;
+        p4[i] = make_double4(x[i], y[i], z[i], (double)o);      // position + octant in one 32-byte record: the reduction gathers one sector per point
         // voxel index relative to the smallest index of the cloud: non-negative, row order unchanged
         uint64_t ix = (uint64_t)((int64_t)f0 - og.lo[0]), iy = (uint64_t)((int64_t)f1 - og.lo[1]), iz = (uint64_t)((int64_t)f2 - og.lo[2]);
         if (wide) {
@@ -67,8 +67,7 @@ struct HeadPredWide {
 
 __global__ void __launch_bounds__(128)
 voxel_reduce_kernel(int64_t V, int64_t n, const int32_t *__restrict__ heads, const uint32_t *__restrict__ order,
-                    const uint8_t *__restrict__ oct,
-                    const double *__restrict__ px, const double *__restrict__ py, const double *__restrict__ pz,
+                    const double4 *__restrict__ p4,
                     const double *__restrict__ nx, const double *__restrict__ ny, const double *__restrict__ nz,
                     const double *__restrict__ cr, const double *__restrict__ cg, const double *__restrict__ cb,
                     int32_t *__restrict__ rep, int32_t *__restrict__ count, double *__restrict__ centroid,
@@ -84,10 +83,11 @@ voxel_reduce_kernel(int64_t V, int64_t n, const int32_t *__restrict__ heads, con
         int32_t last = -1;
         for (int64_t j = j0; j < j1; ++j) {
             uint32_t i = order[j];
-            sp0 = __dadd_rn(sp0, px[i]); sp1 = __dadd_rn(sp1, py[i]); sp2 = __dadd_rn(sp2, pz[i]);
+            const double4 q = p4[i];
+            sp0 = __dadd_rn(sp0, q.x); sp1 = __dadd_rn(sp1, q.y); sp2 = __dadd_rn(sp2, q.z);
             if (nx) { sn0 = __dadd_rn(sn0, nx[i]); sn1 = __dadd_rn(sn1, ny[i]); sn2 = __dadd_rn(sn2, nz[i]); }
             if (cr) { sc0 = __dadd_rn(sc0, cr[i]); sc1 = __dadd_rn(sc1, cg[i]); sc2 = __dadd_rn(sc2, cb[i]); }
-            int o = oct[i];
+            int o = (int)q.w;
 #pragma unroll
             for (int k = 0; k < 8; ++k) if (k == o) cub[k] = (int32_t)i;
             last = (int32_t)i;
@@ -164,7 +164,7 @@ static int voxel_impl(o3dpp_ctx *c, double voxel_size, const double *min3, const
     size_t nn = (size_t)n + 64;
     O3_TRY(c->s_keys0.ensure(nn * 8)); O3_TRY(c->s_keys1.ensure(nn * 8));
     O3_TRY(c->s_vals0.ensure(nn * 4)); O3_TRY(c->s_vals1.ensure(nn * 4));
-    O3_TRY(c->v_oct.ensure(nn)); O3_TRY(c->v_order.ensure(nn * 4)); O3_TRY(c->v_seg.ensure(nn * 4));
+    O3_TRY(c->g_p4.ensure(nn * 32)); O3_TRY(c->v_order.ensure(nn * 4)); O3_TRY(c->v_seg.ensure(nn * 4));
     DevBuf wide_lo, wide_ix;
     uint64_t *key_lo = c->s_keys0.as<uint64_t>();
     uint32_t *key_ix = nullptr;
@@ -175,7 +175,7 @@ static int voxel_impl(o3dpp_ctx *c, double voxel_size, const double *min3, const
     }
     int grid = grid_for(c, n, 256, 16);
     LAUNCH(c, voxel_key_kernel, grid, 256, 0, c->pts.x(), c->pts.y(), c->pts.z(), n, og,
-           voxel_size, pk, wide, key_lo, key_ix, c->v_oct.as<uint8_t>());
+           voxel_size, pk, wide, key_lo, key_ix, c->g_p4.as<double4>());
     O3_TRY(check_launch("voxel_key"));
     uint64_t *ks = nullptr;
     uint32_t *vs = nullptr;
@@ -209,7 +209,7 @@ static int voxel_impl(o3dpp_ctx *c, double voxel_size, const double *min3, const
     CU_TRY(cudaMemsetAsync(flags.p, 0, nn, c->stream));
     bool hn = c->nrm.present, hc = c->col.present;
     LAUNCH(c, voxel_reduce_kernel, grid_for(c, V, 128, 32), 128, 0, V, n, heads, c->v_order.as<uint32_t>(),
-           c->v_oct.as<uint8_t>(), c->pts.x(), c->pts.y(), c->pts.z(),
+           c->g_p4.as<double4>(),
            hn ? c->nrm.x() : nullptr, hn ? c->nrm.y() : nullptr, hn ? c->nrm.z() : nullptr,
            hc ? c->col.x() : nullptr, hc ? c->col.y() : nullptr, hc ? c->col.z() : nullptr,
            c->v_rep.as<int32_t>(), c->v_count.as<int32_t>(), c->v_centroid.as<double>(),

@@ -201,7 +201,8 @@ def slab_estimate_normals(ctx, owned: np.ndarray, axis: int, cuts: Sequence[floa
     owned points alone answers every query whose k-th distance bound (o3dpp_fetch_kth_bound) stays short of
     the cut; the halo width is the largest bound among the others (all-reduce MAX), one exchange, and a
     second pass over just the strips along the cuts (own points within two halo widths + the halo) for those
-    queries.  Returns (normals of the owned points, info dict).  The context is left holding the owned points
+    queries.  Exact ties in d2 at the k-th neighbour are broken by LOCAL index (owned points first, then halo), which can pick
+    another member of the tie than the whole-scan call does.  Returns (normals of the owned points, info dict).  The context is left holding the owned points
     first (hybrid / radius: followed by the halo)."""
     from . import _native as nat
     owned = np.ascontiguousarray(owned, dtype=np.float64).reshape(-1, 3)
@@ -212,6 +213,9 @@ def slab_estimate_normals(ctx, owned: np.ndarray, axis: int, cuts: Sequence[floa
         ctx.drop(nat.ATTR_NORMALS)
         ctx.estimate_normals(mode, knn, radius)
         return _download_normals(ctx, n_own), info
+    if mode == nat.SEARCH_KNN and knn > 32:
+        raise ValueError("slab-sharded pure KNN needs knn <= 32 (the k-th distance bounds come from the certified selection path); "
+                         "use KDTreeSearchParamHybrid(radius, max_nn) for larger neighbourhoods")
     if mode == nat.SEARCH_KNN:
         # pass 1: the owned points alone.  A query whose k-th distance bound r stays short of the cut already has its global
         # neighbours (safe); the others need the points of the neighbour slabs within r of the cut
@@ -246,8 +250,11 @@ def slab_estimate_normals(ctx, owned: np.ndarray, axis: int, cuts: Sequence[floa
             ctx.upload(nat.ATTR_POINTS, owned)          # the context is left holding the owned points (slab_segment_plane)
             ctx.drop(nat.ATTR_NORMALS)
             return nrm, info
-        # a slab with fewer than k points: no bound at all; one pass over everything with a halo as wide as the scan
-        halo_w = float(_allreduce(np.array([np.ptp(owned[:, axis]) if n_own else 0.0]), "sum", group)[0]) + 1.0
+        # a slab with fewer than k points: no bound at all; one pass over everything with a halo as wide as the whole scan
+        # (global extent along the axis: empty gaps between the slabs count too)
+        lo = float(_allreduce(np.array([owned[:, axis].min() if n_own else np.inf]), "min", group)[0])
+        hi = float(_allreduce(np.array([owned[:, axis].max() if n_own else -np.inf]), "max", group)[0])
+        halo_w = (hi - lo) + 1.0
         info["passes"] = 2
     else:
         halo_w = float(radius)
@@ -613,6 +620,9 @@ def dev_slab_estimate_normals(ctx, owned, axis: int, cuts, rank: int, world: int
                     exchange_ms=(time.perf_counter() - t0) * 1e3)
         return halo
 
+    if world > 1 and mode == nat.SEARCH_KNN and knn > 32:
+        raise ValueError("slab-sharded pure KNN needs knn <= 32 (the k-th distance bounds come from the certified selection path); "
+                         "use KDTreeSearchParamHybrid(radius, max_nn) for larger neighbourhoods")
     if world > 1 and mode == nat.SEARCH_KNN:
         # the same two passes as slab_estimate_normals: all owned points alone, then only the strips along the cuts for the
         # queries whose k-th distance bound reaches across a cut
@@ -644,8 +654,9 @@ def dev_slab_estimate_normals(ctx, owned, axis: int, cuts, rank: int, world: int
                 ctx.upload_dev(nat.ATTR_POINTS, owned.contiguous().data_ptr(), n_own, nat.F64)   # left holding the owned points
                 ctx.drop(nat.ATTR_NORMALS)
             return nrm, info
-        span = float(owned[:, axis].max() - owned[:, axis].min()) if n_own else 0.0
-        halo_w = float(_allreduce(np.array([span]), "sum", group)[0]) + 1.0
+        lo = float(_allreduce(np.array([float(owned[:, axis].min()) if n_own else np.inf]), "min", group)[0])
+        hi = float(_allreduce(np.array([float(owned[:, axis].max()) if n_own else -np.inf]), "max", group)[0])
+        halo_w = (hi - lo) + 1.0
         info["passes"] = 2
     else:
         halo_w = float(radius) if world > 1 else 0.0

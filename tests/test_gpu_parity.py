@@ -53,6 +53,48 @@ def test_transform_bit_exact(ctx, orc, bunny, n):
     ctx.drop(nat.ATTR_NORMALS)
 
 
+def test_transform_affine_fast_path_and_non_finite(ctx, orc):
+    """affine T: the division by w == 1.0 is skipped (r / 1.0 == r bit for bit); a non-finite coordinate makes w NaN and
+    takes the division, so the result is the oracle's NaN pattern too"""
+    rng = np.random.default_rng(17)
+    pts = rng.normal(scale=50.0, size=(1001, 3))
+    pts[5] = [np.inf, 1.0, 2.0]
+    pts[77] = [0.5, np.nan, -3.0]
+    pts[500] = [1e308, -1e308, 1e308]
+    T = _rand_T(rng)
+    ctx.upload(nat.ATTR_POINTS, pts)
+    ctx.transform(T)
+    with np.errstate(all="ignore"):
+        ep, _ = orc.transform(pts, T)
+    got = ctx.download(nat.ATTR_POINTS)
+    assert np.array_equal(got, ep, equal_nan=True)
+    assert np.array_equal(np.isnan(got), np.isnan(ep))
+
+
+def test_transform_points_leaves_normals(ctx, orc, bunny):
+    """o3dpp_transform_points: PlaneNormalize rotates pcd[:, :3] only (reference processors.py:725-744)"""
+    rng = np.random.default_rng(18)
+    nrm = rng.normal(size=bunny.shape)
+    T = _rand_T(rng)
+    ctx.upload(nat.ATTR_POINTS, bunny)
+    ctx.upload(nat.ATTR_NORMALS, nrm)
+    ctx.transform_points(T)
+    assert np.array_equal(ctx.download(nat.ATTR_POINTS), orc.transform(bunny, T)[0])
+    assert np.array_equal(ctx.download(nat.ATTR_NORMALS), nrm)
+    rows = np.empty((len(bunny), 6))
+    ctx.download_rows6(rows)
+    assert np.array_equal(rows[:, :3], orc.transform(bunny, T)[0]) and np.array_equal(rows[:, 3:], nrm)
+    r32 = np.empty((len(bunny), 6), np.float32)
+    ctx.download_rows6(r32)
+    assert np.array_equal(r32, rows.astype(np.float32))
+    ctx.drop(nat.ATTR_NORMALS)
+
+
+def test_fp64_peak_is_plausible(ctx):
+    tf = ctx.fp64_peak()
+    assert 5.0 < tf < 200.0          # B200: ~34 TFLOP/s of FP64 FMA measured
+
+
 # ------------------------------------------------------------------ voxel
 def _check_voxel(ctx, orc, pts, vs, normals=None, colors=None):
     ctx.upload(nat.ATTR_POINTS, pts)
