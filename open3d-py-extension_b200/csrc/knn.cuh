@@ -26,6 +26,9 @@
 #include <stdlib.h>
 
 #define KNN_MAX_LEVELS 6
+#ifndef KNN_NEAREST_FIRST
+#define KNN_NEAREST_FIRST 1
+#endif
 
 struct GridDesc {
     int64_t n;
@@ -443,9 +446,25 @@ struct Search {
         double lb = ex ? box_lb(LVL, c) : pos_inf();
         unsigned m = __ballot_sync(FULL, ex && lb <= bound);
         st_visit++;
+#if KNN_NEAREST_FIRST
+        const unsigned nkey = __float_as_uint(__double2float_rd(lb));      // non-negative: the bit patterns order like the values
+#endif
         while (m) {
+#if KNN_NEAREST_FIRST
+            // nearest child first (MODE 1 sums everything inside the radius: the order is irrelevant there): the bound tightens
+            // early and the far children, which a walk in index order would open and insert from, are never touched
+            int b;
+            if (MODE == 1) b = __ffs(m) - 1;
+            else {
+                const bool mine = (m >> lane) & 1u;
+                const unsigned kmin = __reduce_min_sync(FULL, mine ? nkey : 0xffffffffu);
+                b = __ffs(__ballot_sync(FULL, mine && nkey == kmin)) - 1;
+            }
+            m &= ~(1u << b);
+#else
             int b = __ffs(m) - 1;
             m &= m - 1;
+#endif
             int64_t child = parent * 32 + b;
             if constexpr (LVL == 0) {
                 if (MODE == 1 || child != home) leaf(child);

@@ -3,7 +3,10 @@
 // Tier 2 (knn_range_kernel): the queries tier 1 could not certify, compacted in curve order; a warp takes 32 of them and
 //   answers one at a time: exact FP64 range query (d2 <= cap, the bound tier 1 left) over the range tables into a shared
 //   list, exact (d2, index) ranking, FP64 cumulants, finish.  List overflow -> tier 3.
-// Tier 3 (knn_exact_kernel): warp per query, the exact FP64 list search of knn.cuh.
+// Tier 3 (knn_exact_kernel): warp per query, the exact FP64 sorted-list search of knn.cuh, nearest child first.
+//   (Measured and not kept: a middle tier with a 1024-entry (d2, position) list and an 8-pass radix select over the FP64 bit
+//   patterns answered 36.6 k of the 49 k overflowing queries of the 10 M scan but left the 12 k with more than 1024 points inside
+//   their bound, which are the expensive ones: 1.21 ms against 0.86 ms of the exact search alone.)
 #pragma once
 #include "knn_select.cuh"
 
@@ -20,9 +23,14 @@
 #endif
 
 struct K2WarpMem {
+    static constexpr int LIST = K2_LIST;
     double d[K2_LIST], x[K2_LIST], y[K2_LIST], z[K2_LIST];
     unsigned oidx[K2_LIST];
     unsigned pos[K2_LIST];      // sorted position (neighbour-set record, keep mode)
+    __device__ __forceinline__ void put(int at, double dd, double xx, double yy, double zz, int64_t p, const GridDesc &g)
+    {
+        d[at] = dd; x[at] = xx; y[at] = yy; z[at] = zz; oidx[at] = g.sidx[p]; pos[at] = (unsigned)p;
+    }
 };
 
 // lower bound (FP32, every step rounded down, boxes stored rounded outwards) of the squared distance from q to box c
@@ -36,15 +44,15 @@ __device__ __forceinline__ float kl_box_lb(const GridDesc &g, int lvl, int64_t c
     return __fadd_rd(__fadd_rd(__fmul_rd(gx, gx), __fmul_rd(gy, gy)), __fmul_rd(gz, gz));
 }
 
-template <int MODE>
+template <int MODE, class Mem>
 struct K2Range {
     const GridDesc &g;
-    K2WarpMem &sm;
+    Mem &sm;
     int lane;
     double qx, qy, qz, cap, r2;
     float fql[3], fqh[3], capf;     // the query rounded down / up and the bound rounded up, for the FP32 box test
     int cnt, K;
-    __device__ __forceinline__ K2Range(const GridDesc &g_, K2WarpMem &sm_) : g(g_), sm(sm_) {}
+    __device__ __forceinline__ K2Range(const GridDesc &g_, Mem &sm_) : g(g_), sm(sm_) {}
 
     __device__ __forceinline__ void leaf(int64_t leaf_id)
     {
@@ -58,7 +66,7 @@ struct K2Range {
         }
         unsigned m = __ballot_sync(FULL, hit);
         int at = cnt + __popc(m & ((1u << lane) - 1u));
-        if (hit && at < K2_LIST) { sm.d[at] = d; sm.x[at] = x; sm.y[at] = y; sm.z[at] = z; sm.oidx[at] = g.sidx[p]; sm.pos[at] = (unsigned)p; }
+        if (hit && at < Mem::LIST) sm.put(at, d, x, y, z, p, g);
         cnt += __popc(m);
     }
 
@@ -72,7 +80,7 @@ struct K2Range {
         // fixed bound: every child that intersects the ball is opened, the order does not matter.  (Opening the nearest child
         // first and shrinking the bound to the k-th distance whenever the list fills was measured twice: as a replacement, and
         // as a middle tier for the 49 k overflowing queries of the 10 M scan, 2.2 ms against 1.2 ms of the exact search.)
-        while (m && cnt <= K2_LIST) {
+        while (m && cnt <= Mem::LIST) {
             const int b = __ffs(m) - 1;
             m &= m - 1;
             if constexpr (LVL == 0) leaf(parent * 32 + b);
@@ -115,7 +123,7 @@ knn_range_kernel(const GridDesc g, int K, double radius, KnnOut out, const int32
         float cf = capbuf[myq];
         if (cf < 3.0e38f) mycap = (double)cf;
     }
-    K2Range<MODE> rq(g, sm);
+    K2Range<MODE, K2WarpMem> rq(g, sm);
     rq.lane = lane; rq.K = K;
     rq.r2 = __dmul_rn(radius, radius);
     Cumul mine;
