@@ -116,7 +116,9 @@ __device__ __forceinline__ float kf_err(float t, float eA, float eC)
 // Thread per query, the K gathers in batches of KC_UNR.  Measured at 10 M and not kept: a lane PAIR per 32-byte record (16 + 16
 // bytes in one instruction, to halve the L1 wavefronts) 2.16 ms against 1.58 (the kernel is latency bound, not wavefront bound);
 // running it on a second stream beside tiers 2 and 3 (it fills the register file: the kernels serialise anyway).
-// 64 registers (KC_MINB 8) against 88: 1.30 against 1.58 ms.
+// 64 registers (KC_MINB 8) against 88: 1.30 against 1.58 ms.  Also measured without gain: prefetch.global.L1 of all K records before the
+// loop (2.04 ms), FMAs in the cumulants (1.31), reciprocal multiplications for the ~20 divisions by a common denominator in the
+// covariance and the eigen-solve (1.40 ms, and the 1e-7 agreement with the oracle on well-conditioned points is lost).
 #ifndef KC_MINB
 #define KC_MINB 8       // resident 128-thread blocks per SM the register budget is set for
 #endif
