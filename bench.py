@@ -350,6 +350,18 @@ def run_c5(ctx, nat, rank, world, local, dist, barrier, total):
     out["cut_redistribute_ms"] = _max_over_ranks([t_red * 1e3], dist, local)[0]
     out["voxel"] = {"ms": _max_over_ranks([t_vox * 1e3], dist, local)[0], "voxels_total": vres["V_total"], "collectives": "all-reduce(min) of 6 doubles + all-gather of the row counts; no halo"}
     out["redistribution_bytes_upper_bound_per_rank"] = moved * 24
+    # transform: every rank maps its own slab in place, no collective
+    T = np.eye(4); T[:3, :3] = np.linalg.qr(np.random.default_rng(3).normal(size=(3, 3)))[0]; T[:3, 3] = (0.5, -1.0, 0.25)
+    Ti = np.linalg.inv(T)
+    ctx.upload_dev(nat.ATTR_POINTS, owned.data_ptr(), len(owned))
+    for M in (T, Ti, T, Ti):                  # warm-up, back to the start
+        ctx.transform(M)
+    ctx.synchronize(); barrier(); t0 = time.perf_counter()
+    for M in (T, Ti, T, Ti, T, Ti):
+        ctx.transform(M)
+    ctx.synchronize(); barrier(); t_tr = (time.perf_counter() - t0) / 6
+    t_tr = _max_over_ranks([t_tr * 1e3], dist, local)[0]
+    out["transform"] = {"ms": t_tr, "achieved_gbs_whole_job": total * 48 / (t_tr * 1e-3) / 1e9, "collectives": "none"}
     for name, mode in (("hybrid", nat.SEARCH_HYBRID), ("knn", nat.SEARCH_KNN)):
         rows = []
         for step in range(2):                 # first pass = warm-up (buffer growth)

@@ -115,6 +115,14 @@ def _worker(rank, world, port, q):
         assert np.array_equal(mine_v[vres["rep"]].shape, (vres["V"], 3))
         out["vox"] = sh.gather_voxel_rows(vres, rank, world)
         out["vox_local"] = (vres["V"], vres["row_offset"], vres["V_total"], vaxis)
+        # transform: every rank maps its own rows, no exchange
+        T = np.eye(4); T[:3, :3] = np.linalg.qr(np.random.default_rng(9).normal(size=(3, 3)))[0]; T[:3, 3] = (1.5, -2.0, 0.25)
+        ctx.upload(nat.ATTR_POINTS, owned)
+        ctx.transform(T)
+        moved = np.empty_like(owned)
+        ctx.download(nat.ATTR_POINTS, moved)
+        out["transformed"] = moved
+        out["T"] = T
         ctx.close()
         q.put((rank, "ok", out))
     except Exception:   # noqa: BLE001
@@ -174,3 +182,6 @@ def test_world2_slabs_equal_single_context(ctx):
         assert np.abs(vx["centroid"] - ref["centroid"]).max() <= 1e-5 * np.abs(ref["centroid"]).max()      # north_star bar; sums differ in order only
         assert np.abs(vx["centroid"] - one["centroid"]).max() <= 1e-12 * np.abs(ref["centroid"]).max()
     assert o0["vox_local"][0] + o1["vox_local"][0] == V and o0["vox_local"][1] == 0 and o1["vox_local"][1] == o0["vox_local"][0]
+    # sharded transform: the concatenation of the ranks' rows is bit-equal to the oracle's transform of the whole scan
+    assert np.array_equal(o0["T"], o1["T"])
+    assert np.array_equal(np.concatenate([o0["transformed"], o1["transformed"]], 0), orc.transform(whole, o0["T"])[0])
