@@ -116,6 +116,19 @@ O3DPP_API int o3dpp_has(o3dpp_ctx *ctx, int attr, int *flag);
 O3DPP_API int o3dpp_drop(o3dpp_ctx *ctx, int attr);
 /* pcd.get_min_bound() / get_max_bound() (PointCloud.py:340): 3 + 3 float64 */
 O3DPP_API int o3dpp_bounds(o3dpp_ctx *ctx, double *min3, double *max3);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same min / max bound as o3dpp_bounds
+ * (bit-equal: min and max do not depend on the reduction order), but it allocates nothing and needs no context:
+ *   dev_rows  n x 3 float64, row-major, DEVICE memory on `device` (the layout o3dpp_upload_dev takes);
+ *   dev_out6  6 float64 of DEVICE memory: min x y z, max x y z (zeros for n = 0, as o3dpp_bounds answers);
+ *   stream    a cudaStream_t of `device` (0 = the default stream); the call only enqueues, it does not synchronise.
+ * The per-block partial bounds live in a file-scope __device__ array of 768 KiB that every GPU loading the library holds
+ * until exit; n > O3DPP_BOUNDS_STATIC_MAX_POINTS is refused with O3DPP_E_ARG (use o3dpp_bounds).  No cudaMalloc, cudaFree
+ * or allocating library routine is called.  All calls on one device share the array, so calls that overlap on the GPU
+ * (two streams, two threads) race: keep them on one stream or order them with events.  The first call per device resolves
+ * the array's address (cudaGetSymbolAddress): make it once before capturing a graph. */
+#define O3DPP_BOUNDS_STATIC_MAX_POINTS 67108864LL    /* 2^26 points = 16 384 tiles of 4 096 rows x 48 B of scratch */
+O3DPP_API int o3dpp_bounds_static(int device, uintptr_t stream, uintptr_t dev_rows, int64_t n, uintptr_t dev_out6);
 
 /* ---- transform: replaces pcd.transform(T) (PointCloud.py:60-62) ------------------ */
 /* T = 16 float64 row-major.  points: (T[p,1]).xyz / w ; normals (if present): (T[n,0]).xyz */

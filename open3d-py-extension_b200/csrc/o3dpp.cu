@@ -4,6 +4,7 @@
 // There is no CPU path in this library: every entry point needs a live CUDA context.
 #include "extras.cuh"
 #include <stdlib.h>
+#include <mutex>
 
 #define CTX_CHECK(c)                                                      \
     do {                                                                  \
@@ -427,4 +428,140 @@ O3DPP_API int o3dpp_zsplat(o3dpp_ctx *c, int grid_size, double x_min, double x_m
     CTX_CHECK(c);
     if (!z_grid) return set_err(O3DPP_E_ARG, "null argument");
     return zsplat_impl(c, grid_size, x_min, x_max, y_min, y_max, z_grid, last_index);
+}
+
+/* ---- o3dpp_bounds_static: min/max bound with NO allocation ------------------------------------------------------------
+ * No counterpart in the reference; added for callers that cannot call cudaMalloc
+ * (CUDA graph capture, tight serving loops).  Same result as o3dpp_bounds, but context-free: input and output are the
+ * caller's device buffers, the per-block partial bounds live in a file-scope __device__ array of fixed size that every
+ * GPU loading the library holds until exit.  Fixed tiles of SB_TILE rows per block (no grid-stride loop), so the scratch
+ * a call needs is ceil(n / SB_TILE) x 6 doubles and n is bounded by O3DPP_BOUNDS_STATIC_MAX_POINTS.
+ * Nothing in the scratch has to start at zero: the final kernel reads exactly the slots the partial kernel of the same
+ * call has written.  Every call on a device shares the array: two calls that overlap on the GPU (different streams) race. */
+#define SB_THREADS 256
+#define SB_ROWS 16                                   /* rows per thread */
+#define SB_TILE (SB_THREADS * SB_ROWS)               /* 4096 rows = 96 KiB of input per block */
+#define SB_MAX_BLOCKS (int)(O3DPP_BOUNDS_STATIC_MAX_POINTS / SB_TILE)
+static_assert(O3DPP_BOUNDS_STATIC_MAX_POINTS % SB_TILE == 0, "whole tiles");
+#define SB_MAX_DEVICES 64
+
+static __device__ __align__(256) double g_static_bounds_part[(size_t)SB_MAX_BLOCKS * 6];      /* 768 KiB */
+
+// rows are interleaved (x y z x y z ...): the tile is read as 3 * SB_TILE consecutive doubles, thread t takes elements
+// t, t + 256, ...; 256 = 1 (mod 3), so element j of a thread belongs to coordinate (t + j) mod 3: three accumulator
+// pairs indexed by j mod 3 at compile time, rotated to (x, y, z) once at the end
+__global__ void __launch_bounds__(SB_THREADS)
+bounds_static_partial_kernel(const double *__restrict__ rows, int64_t n, double *__restrict__ part)
+{
+    const int64_t e0 = (int64_t)blockIdx.x * (3 * SB_TILE), e1 = 3 * n;     // flat element range of this tile
+    const double *p = rows + e0;
+    int64_t left = e1 - e0;                                                 // > 0: the grid is ceil(n / SB_TILE)
+    int t = threadIdx.x, t3 = t % 3;
+    double lo[3], hi[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {                                           // start from a real element of the same coordinate
+        int64_t e = t + SB_THREADS * r;
+        if (e >= left) e = (t3 + r) % 3;                                    // element (t3 + r) % 3 of row 0 of the tile
+        lo[r] = hi[r] = p[e];
+    }
+#pragma unroll
+    for (int j = 0; j < 3 * SB_ROWS; ++j) {
+        int64_t e = t + SB_THREADS * j;
+        if (e < left) {
+            double v = p[e];
+            if (v < lo[j % 3]) lo[j % 3] = v;
+            if (v > hi[j % 3]) hi[j % 3] = v;
+        }
+    }
+    double mn[3], mx[3];                                                    // accumulator r holds coordinate (t3 + r) % 3
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        int r = (k - t3 + 3) % 3;
+        mn[k] = r == 0 ? lo[0] : r == 1 ? lo[1] : lo[2];
+        mx[k] = r == 0 ? hi[0] : r == 1 ? hi[1] : hi[2];
+    }
+    __shared__ double sh[SB_THREADS / 32][6];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            double o = shfl_xor_d(mn[k], d);
+            if (o < mn[k]) mn[k] = o;
+            o = shfl_xor_d(mx[k], d);
+            if (o > mx[k]) mx[k] = o;
+        }
+    }
+    if (lane_id() == 0) {
+        for (int k = 0; k < 3; ++k) { sh[t >> 5][k] = mn[k]; sh[t >> 5][3 + k] = mx[k]; }
+    }
+    __syncthreads();
+    if (t < 6) {
+        double v = sh[0][t];
+        for (int w = 1; w < SB_THREADS / 32; ++w) {
+            double o = sh[w][t];
+            if (t < 3 ? o < v : o > v) v = o;
+        }
+        part[(int64_t)blockIdx.x * 6 + t] = v;
+    }
+}
+
+// one block of 6 warps: warp k reduces column k of the `blocks` partial rows
+__global__ void __launch_bounds__(192)
+bounds_static_final_kernel(const double *__restrict__ part, int blocks, double *__restrict__ out6)
+{
+    int k = threadIdx.x >> 5, lane = lane_id();
+    double v = part[k];
+    for (int b = lane; b < blocks; b += 32) {
+        double o = part[(int64_t)b * 6 + k];
+        if (k < 3 ? o < v : o > v) v = o;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        double o = shfl_xor_d(v, d);
+        if (k < 3 ? o < v : o > v) v = o;
+    }
+    if (lane == 0) out6[k] = v;
+}
+
+// the array's name is a host-side stand-in in host code: the device address is resolved once per device, with that
+// device current, and handed to the kernels as an ordinary pointer
+static double *g_static_bounds_addr[SB_MAX_DEVICES];
+static std::mutex g_static_bounds_mutex;
+
+static int static_bounds_scratch(int device, double **out)
+{
+    std::lock_guard<std::mutex> lk(g_static_bounds_mutex);
+    if (!g_static_bounds_addr[device]) {
+        double *ptr = nullptr;
+        CU_TRY(cudaGetSymbolAddress((void **)&ptr, g_static_bounds_part));
+        if (!ptr) return set_err(O3DPP_E_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+        g_static_bounds_addr[device] = ptr;
+    }
+    *out = g_static_bounds_addr[device];
+    return 0;
+}
+
+O3DPP_API int o3dpp_bounds_static(int device, uintptr_t stream, uintptr_t dev_rows, int64_t n, uintptr_t dev_out6)
+{
+    if (device < 0 || device >= SB_MAX_DEVICES) return set_err(O3DPP_E_ARG, "o3dpp_bounds_static: device index out of range");
+    if (n < 0) return set_err(O3DPP_E_ARG, "o3dpp_bounds_static: negative point count");
+    if (n > O3DPP_BOUNDS_STATIC_MAX_POINTS) {
+        char b[256];
+        snprintf(b, sizeof b, "o3dpp_bounds_static: %lld points exceed the static scratch (O3DPP_BOUNDS_STATIC_MAX_POINTS = %lld); use o3dpp_bounds",
+                 (long long)n, (long long)O3DPP_BOUNDS_STATIC_MAX_POINTS);
+        return set_err(O3DPP_E_ARG, b);
+    }
+    if (!dev_out6 || (n > 0 && !dev_rows)) return set_err(O3DPP_E_ARG, "o3dpp_bounds_static: null device pointer");
+    CU_TRY(cudaSetDevice(device));
+    cudaStream_t s = (cudaStream_t)stream;
+    if (n == 0) {                                     // o3dpp_bounds answers zeros for an empty cloud
+        CU_TRY(cudaMemsetAsync((void *)dev_out6, 0, 6 * sizeof(double), s));
+        return 0;
+    }
+    double *part = nullptr;
+    O3_TRY(static_bounds_scratch(device, &part));
+    int blocks = (int)((n + SB_TILE - 1) / SB_TILE);
+    bounds_static_partial_kernel<<<blocks, SB_THREADS, 0, s>>>((const double *)dev_rows, n, part);
+    bounds_static_final_kernel<<<1, 192, 0, s>>>(part, blocks, (double *)dev_out6);
+    return check_launch("bounds_static");
 }

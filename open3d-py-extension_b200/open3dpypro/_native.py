@@ -34,6 +34,7 @@ SYMBOLS = [
     "o3dpp_plane_inliers", "o3dpp_inlier_moments", "o3dpp_fetch_kth_bound", "o3dpp_knn_mean_distance", "o3dpp_zsplat", "o3dpp_download_async",
     "o3dpp_set_option", "o3dpp_fetch_neighbors", "o3dpp_voxel_bounded", "o3dpp_download_as", "o3dpp_download_rows6",
     "o3dpp_host_register", "o3dpp_host_unregister", "o3dpp_fp64_peak", "o3dpp_transform_points",
+    "o3dpp_bounds_static",
 ]
 
 _lib = None
@@ -79,6 +80,15 @@ def device_count():
     n = C.c_int(0)
     _check(lib().o3dpp_device_count(C.byref(n)))
     return n.value
+
+
+BOUNDS_STATIC_MAX_POINTS = 1 << 26      # O3DPP_BOUNDS_STATIC_MAX_POINTS of include/o3dpp.h
+
+
+def bounds_static(device, dev_rows, n, dev_out6, stream=0):
+    """o3dpp_bounds_static: min / max bound of n x 3 float64 device rows into 6 device doubles without any allocation
+    (static device scratch, n <= BOUNDS_STATIC_MAX_POINTS); enqueues on `stream` and returns"""
+    _check(lib().o3dpp_bounds_static(C.c_int(device), C.c_size_t(stream), C.c_size_t(dev_rows), C.c_int64(n), C.c_size_t(dev_out6)))
 
 
 def _ptr(a):
