@@ -122,6 +122,7 @@ struct o3dpp_ctx {
     DevBuf g_sx, g_sy, g_sz, g_sp4, g_sidx, g_box, g_boxf, g_nbr, g_nd2, g_ncnt;
     DevBuf g_p4;                          // the points as (x, y, z, w) 32-byte records in original order: gather source of grid build / voxel
     DevBuf g_glist, g_gcnt;               // tier 1: cell-group lists of knn_groups_kernel
+    DevBuf g_park;                        // tier 2: cumulants of the answered queries, [11][failed queries]
     DevBuf g_nbrpos, g_tier, g_inv;       // tier chain: neighbour positions [K][pitch], answering tier, original index -> position
     bool nbr_valid = false;               // g_nbrpos / g_tier hold the sets of the last estimate_normals (keep mode)
     int nbr_K = 0, nbr_mode = 0;

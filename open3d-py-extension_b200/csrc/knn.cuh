@@ -40,7 +40,9 @@ struct GridDesc {
     const double4 *sp4;               // the same points as (x, y, z, 0) records: one 32-byte sector per gather
     const uint32_t *sidx;             // sorted position -> original index
     const double *box;
-    const float *boxf;                // the same boxes in FP32, rounded outwards (lo down, hi up): conservative culling
+    const float4 *boxq;               // the same boxes in FP32, rounded outwards (lo down, hi up): conservative culling;
+                                      // two records per entry {lo.x lo.y lo.z hi.x} {hi.y hi.z - -}, entry e of table l at qoff[l] + e
+    int qoff[KNN_MAX_LEVELS];
 };
 
 // ---- build -------------------------------------------------------------------------------
@@ -124,7 +126,7 @@ __device__ __forceinline__ double warp_max_d(double v)
 
 // one warp per entry of table `lvl`; children are points (lvl 0) or entries of table lvl-1
 __global__ void __launch_bounds__(256)
-box_level_kernel(GridDesc g, int lvl, double *__restrict__ box, float *__restrict__ boxf)
+box_level_kernel(GridDesc g, int lvl, double *__restrict__ box, float4 *__restrict__ boxq)
 {
     int64_t node = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (node >= g.cnt[lvl]) return;
@@ -147,9 +149,9 @@ box_level_kernel(GridDesc g, int lvl, double *__restrict__ box, float *__restric
         int64_t p = g.pitch[lvl];
         b[node] = lo[0]; b[p + node] = lo[1]; b[2 * p + node] = lo[2];
         b[3 * p + node] = hi[0]; b[4 * p + node] = hi[1]; b[5 * p + node] = hi[2];
-        float *bf = boxf + g.off[lvl];
-        bf[node] = __double2float_rd(lo[0]); bf[p + node] = __double2float_rd(lo[1]); bf[2 * p + node] = __double2float_rd(lo[2]);
-        bf[3 * p + node] = __double2float_ru(hi[0]); bf[4 * p + node] = __double2float_ru(hi[1]); bf[5 * p + node] = __double2float_ru(hi[2]);
+        float4 *bq = boxq + 2 * ((int64_t)g.qoff[lvl] + node);
+        bq[0] = make_float4(__double2float_rd(lo[0]), __double2float_rd(lo[1]), __double2float_rd(lo[2]), __double2float_ru(hi[0]));
+        bq[1] = make_float4(__double2float_ru(hi[1]), __double2float_ru(hi[2]), 0.f, 0.f);
     }
 }
 
@@ -657,6 +659,7 @@ static int grid_build(o3dpp_ctx *c, GridDesc *gd)
         gd->cnt[L] = cnt;
         gd->pitch[L] = ((cnt + 31) / 32) * 32;
         gd->off[L] = off;
+        gd->qoff[L] = (int)(off / 6);
         off += gd->pitch[L] * 6;
         ++L;
         if (cnt <= 32 || L == KNN_MAX_LEVELS) break;
@@ -665,16 +668,17 @@ static int grid_build(o3dpp_ctx *c, GridDesc *gd)
     if (gd->cnt[L - 1] > 32) return set_err(O3DPP_E_UNSUPPORTED, "cloud too large for the range-table depth");
     gd->levels = L;
     O3_TRY(c->g_box.ensure((size_t)off * 8 + 256));
-    O3_TRY(c->g_boxf.ensure((size_t)off * 4 + 256));
+    if (off / 6 > 0x3fffffff) return set_err(O3DPP_E_UNSUPPORTED, "cloud too large for 32-bit range-table indices");
+    O3_TRY(c->g_boxf.ensure((size_t)(off / 6) * 32 + 256));
     gd->sx = c->g_sx.as<double>(); gd->sy = c->g_sy.as<double>(); gd->sz = c->g_sz.as<double>();
     gd->sidx = c->g_sidx.as<uint32_t>();
     gd->sp4 = c->g_sp4.as<double4>();
     gd->box = c->g_box.as<double>();
-    gd->boxf = c->g_boxf.as<float>();
+    gd->boxq = c->g_boxf.as<float4>();
     for (int l = 0; l < L; ++l) {
         int64_t warps = gd->cnt[l];
         int blocks = (int)((warps * 32 + 255) / 256);
-        LAUNCH(c, box_level_kernel, blocks, 256, 0, *gd, l, c->g_box.as<double>(), c->g_boxf.as<float>());
+        LAUNCH(c, box_level_kernel, blocks, 256, 0, *gd, l, c->g_box.as<double>(), c->g_boxf.as<float4>());
     }
     return check_launch("grid_build");
 }

@@ -73,7 +73,9 @@ static int launch_lane(o3dpp_ctx *c, const GridDesc &gd, int K, double radius, K
         int qpw = (int)(m2 / ((int64_t)c->sm_count * 32));
         qpw = qpw < 2 ? 2 : (qpw > 32 ? 32 : qpw);
         int64_t warps2 = (m2 + qpw - 1) / qpw;
-        LAUNCH(c, k2, (int)((warps2 + K2_WARPS - 1) / K2_WARPS), K2_WARPS * 32, 0, gd, K, radius, out, list, (int)m2, capbuf, qpw);
+        O3_TRY(c->g_park.ensure((size_t)m2 * 11 * sizeof(double) + 256));
+        LAUNCH(c, k2, (int)((warps2 + K2_WARPS - 1) / K2_WARPS), K2_WARPS * 32, 0, gd, K, radius, out, list, (int)m2, capbuf, qpw, c->g_park.as<double>());
+        LAUNCH(c, knn_range_finish_kernel<MODE>, (int)((m2 + 127) / 128), 128, 0, gd, out, list, (int)m2, capbuf, c->g_park.as<double>());
         O3_TRY(check_launch("knn_range"));
         cudaEventRecord(c->ev[5], c->stream);
         O3_TRY(compact_indices(c, pred, n, list, &m3));

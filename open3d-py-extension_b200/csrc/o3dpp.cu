@@ -68,7 +68,7 @@ O3DPP_API int o3dpp_destroy(o3dpp_ctx *c)
                       &c->s_vals0, &c->s_vals1, &c->s_hist, &c->s_scan, &c->s_scan2, &c->s_flags, &c->v_order,
                       &c->v_seg, &c->v_oct, &c->v_rep, &c->v_rep_asc, &c->v_count, &c->v_centroid, &c->v_normal,
                       &c->v_color, &c->v_cubic, &c->g_sx, &c->g_sy, &c->g_sz, &c->g_sidx, &c->g_box, &c->g_nbr,
-                      &c->g_nd2, &c->g_ncnt, &c->g_sp4, &c->g_boxf, &c->g_nbrpos, &c->g_tier, &c->g_inv, &c->g_glist, &c->g_gcnt, &c->g_p4, &c->r_samples, &c->r_planes, &c->r_cnt, &c->r_err, &c->r_inl, &c->r_part};
+                      &c->g_nd2, &c->g_ncnt, &c->g_sp4, &c->g_boxf, &c->g_nbrpos, &c->g_tier, &c->g_inv, &c->g_glist, &c->g_gcnt, &c->g_p4, &c->g_park, &c->r_samples, &c->r_planes, &c->r_cnt, &c->r_err, &c->r_inl, &c->r_part};
     for (DevBuf *b : bufs) b->release();
     if (c->h_small) cudaFreeHost(c->h_small);
     for (int i = 0; i < O3_NEV; ++i) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
