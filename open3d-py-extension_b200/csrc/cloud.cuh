@@ -255,17 +255,22 @@ bounds_partial_kernel(const double *__restrict__ x, const double *__restrict__ y
     }
 }
 
-__global__ void bounds_final_kernel(const double *__restrict__ part, int blocks, double *__restrict__ out6)
+// one block of 6 warps: warp k reduces column k of the partial rows (a single thread walking them cost 42 us at 592 rows)
+__global__ void __launch_bounds__(192)
+bounds_final_kernel(const double *__restrict__ part, int blocks, double *__restrict__ out6)
 {
-    int k = threadIdx.x;
-    if (k < 6) {
-        double v = part[k];
-        for (int b = 1; b < blocks; ++b) {
-            double o = part[b * 6 + k];
-            if (k < 3 ? o < v : o > v) v = o;
-        }
-        out6[k] = v;
+    const int k = threadIdx.x >> 5, lane = lane_id();
+    double v = part[k];
+    for (int b = lane; b < blocks; b += 32) {
+        double o = part[b * 6 + k];
+        if (k < 3 ? o < v : o > v) v = o;
     }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        double o = shfl_xor_d(v, d);
+        if (k < 3 ? o < v : o > v) v = o;
+    }
+    if (lane == 0) out6[k] = v;
 }
 
 // leaves min/max (6 doubles) at d_small[0..5] on the device, and a host copy in mn/mx if non-null
@@ -281,7 +286,7 @@ static int bounds_impl(o3dpp_ctx *c, double *mn, double *mx)
     int grid = grid_for(c, n, BND_THREADS * 4, 4);
     double *part = c->d_small.as<double>() + 16;  // <= 148*4*6 doubles = 28 KiB
     LAUNCH(c, bounds_partial_kernel, grid, BND_THREADS, 0, c->pts.x(), c->pts.y(), c->pts.z(), n, part);
-    LAUNCH(c, bounds_final_kernel, 1, 32, 0, part, grid, c->d_small.as<double>());
+    LAUNCH(c, bounds_final_kernel, 1, 192, 0, part, grid, c->d_small.as<double>());
     O3_TRY(check_launch("bounds"));
     if (mn || mx) {
         CU_TRY(cudaMemcpyAsync(c->h_small, c->d_small.p, 6 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
@@ -297,6 +302,9 @@ static int bounds_impl(o3dpp_ctx *c, double *mn, double *mx)
 // Geometry3D::TransformPoints / TransformNormals: r = ((T0*x + T1*y) + T2*z) + T3*w, FP64, no FMA.
 // HBM bound: 48 B per point (24 read + 24 written), 96 B with normals.
 struct Mat4 { double m[16]; };
+#ifndef TR_UNR
+#define TR_UNR 1
+#endif
 
 __device__ __forceinline__ double row_dot(const double *r, double x, double y, double z, double w)
 {
@@ -313,26 +321,38 @@ __global__ void __launch_bounds__(256)
 transform_kernel(double *__restrict__ x, double *__restrict__ y, double *__restrict__ z, int64_t n,
                  const __grid_constant__ Mat4 T, int is_normal)
 {
-    // two points per thread through 16-byte accesses (planes are 256 B aligned)
+    // two points per 16-byte access (planes are 256 B aligned) and TR_UNR accesses per plane and step: the loads of a
+    // step are issued together (3 TR_UNR x 16 B in flight per thread), the kernel is bound by HBM latency x bytes in flight
     int64_t n2 = n >> 1;
     double2 *x2 = (double2 *)x, *y2 = (double2 *)y, *z2 = (double2 *)z;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (int64_t)gridDim.x * blockDim.x) {
-        double2 a = x2[i], b = y2[i], cc = z2[i];
-        double2 ox, oy, oz;
-        if (is_normal) {
-            ox.x = row_dot(T.m + 0, a.x, b.x, cc.x, 0.0); ox.y = row_dot(T.m + 0, a.y, b.y, cc.y, 0.0);
-            oy.x = row_dot(T.m + 4, a.x, b.x, cc.x, 0.0); oy.y = row_dot(T.m + 4, a.y, b.y, cc.y, 0.0);
-            oz.x = row_dot(T.m + 8, a.x, b.x, cc.x, 0.0); oz.y = row_dot(T.m + 8, a.y, b.y, cc.y, 0.0);
-        } else {
-            double w0 = row_dot(T.m + 12, a.x, b.x, cc.x, 1.0), w1 = row_dot(T.m + 12, a.y, b.y, cc.y, 1.0);
-            ox.x = persp(row_dot(T.m + 0, a.x, b.x, cc.x, 1.0), w0);
-            ox.y = persp(row_dot(T.m + 0, a.y, b.y, cc.y, 1.0), w1);
-            oy.x = persp(row_dot(T.m + 4, a.x, b.x, cc.x, 1.0), w0);
-            oy.y = persp(row_dot(T.m + 4, a.y, b.y, cc.y, 1.0), w1);
-            oz.x = persp(row_dot(T.m + 8, a.x, b.x, cc.x, 1.0), w0);
-            oz.y = persp(row_dot(T.m + 8, a.y, b.y, cc.y, 1.0), w1);
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n2; i0 += TR_UNR * stride) {
+        double2 a[TR_UNR], b[TR_UNR], cc[TR_UNR];
+#pragma unroll
+        for (int u = 0; u < TR_UNR; ++u) {
+            const int64_t i = i0 + u * stride;
+            if (i < n2) { a[u] = x2[i]; b[u] = y2[i]; cc[u] = z2[i]; }
         }
-        x2[i] = ox; y2[i] = oy; z2[i] = oz;
+#pragma unroll
+        for (int u = 0; u < TR_UNR; ++u) {
+            const int64_t i = i0 + u * stride;
+            if (i >= n2) break;
+            double2 ox, oy, oz;
+            if (is_normal) {
+                ox.x = row_dot(T.m + 0, a[u].x, b[u].x, cc[u].x, 0.0); ox.y = row_dot(T.m + 0, a[u].y, b[u].y, cc[u].y, 0.0);
+                oy.x = row_dot(T.m + 4, a[u].x, b[u].x, cc[u].x, 0.0); oy.y = row_dot(T.m + 4, a[u].y, b[u].y, cc[u].y, 0.0);
+                oz.x = row_dot(T.m + 8, a[u].x, b[u].x, cc[u].x, 0.0); oz.y = row_dot(T.m + 8, a[u].y, b[u].y, cc[u].y, 0.0);
+            } else {
+                double w0 = row_dot(T.m + 12, a[u].x, b[u].x, cc[u].x, 1.0), w1 = row_dot(T.m + 12, a[u].y, b[u].y, cc[u].y, 1.0);
+                ox.x = persp(row_dot(T.m + 0, a[u].x, b[u].x, cc[u].x, 1.0), w0);
+                ox.y = persp(row_dot(T.m + 0, a[u].y, b[u].y, cc[u].y, 1.0), w1);
+                oy.x = persp(row_dot(T.m + 4, a[u].x, b[u].x, cc[u].x, 1.0), w0);
+                oy.y = persp(row_dot(T.m + 4, a[u].y, b[u].y, cc[u].y, 1.0), w1);
+                oz.x = persp(row_dot(T.m + 8, a[u].x, b[u].x, cc[u].x, 1.0), w0);
+                oz.y = persp(row_dot(T.m + 8, a[u].y, b[u].y, cc[u].y, 1.0), w1);
+            }
+            x2[i] = ox; y2[i] = oy; z2[i] = oz;
+        }
     }
     if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
         int64_t i = n - 1;

@@ -23,6 +23,7 @@
 //     smallest eigenvector, sign alignment, scattered store to the original index.
 #pragma once
 #include "voxel.cuh"
+#include "hilbert_lut.cuh"
 #include <stdlib.h>
 
 #define KNN_MAX_LEVELS 6
@@ -78,36 +79,64 @@ __device__ __forceinline__ uint64_t hilbert3(uint32_t x, uint32_t y, uint32_t z,
     return (spread3(X0) << 2) | (spread3(X1) << 1) | spread3(X2);
 }
 
+// the same index through the generated state machine (hilbert_lut.cuh): Morton code, then two octants per table lookup.
+// ~110 instructions per point against ~400 of the bit-twiddling form, which made curve_key_kernel issue bound (62 % of the
+// issue slots, 0.21 ms at 10 M for a 0.10 ms HBM pass, ncu r02y)
+__device__ __forceinline__ uint64_t hilbert3_lut(uint32_t x, uint32_t y, uint32_t z, int bits, const unsigned char *lut1,
+                                                 const unsigned short *lut2)
+{
+    const uint64_t m = (spread3(x) << 2) | (spread3(y) << 1) | spread3(z);
+    unsigned s = 0;
+    uint64_t h = 0;
+    int k = bits;
+    if (k & 1) {
+        --k;
+        const unsigned e = lut1[(unsigned)(m >> (3 * k)) & 7u];
+        h = e & 7u;
+        s = e >> 3;
+    }
+    while (k > 0) {
+        k -= 2;
+        const unsigned e = lut2[s * 64u + ((unsigned)(m >> (3 * k)) & 63u)];
+        h = (h << 6) | (e & 63u);
+        s = e >> 6;
+    }
+    return h;
+}
+
 __global__ void __launch_bounds__(256)
 curve_key_kernel(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
                   int64_t n, const double *__restrict__ mnmx, int bits, uint64_t *__restrict__ keys, double4 *__restrict__ p4)
 {
+    __shared__ unsigned short lut2[HILBERT_STATES * 64];
+    __shared__ unsigned char lut1[8];
+    for (int t = threadIdx.x; t < HILBERT_STATES * 64; t += blockDim.x) lut2[t] = HILBERT_LUT2[t];
+    if (threadIdx.x < 8) lut1[threadIdx.x] = HILBERT_LUT1[threadIdx.x];          // state 0 only: the first step
+    __syncthreads();
     double m0 = mnmx[0], m1 = mnmx[1], m2 = mnmx[2];
     double ext = fmax(fmax(mnmx[3] - m0, mnmx[4] - m1), mnmx[5] - m2);
     double cells = (double)(1u << bits);
     double scale = ext > 0.0 ? cells / (ext * 1.000000001) : 0.0;
     uint32_t cmax = (1u << bits) - 1u;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        double fx = (x[i] - m0) * scale, fy = (y[i] - m1) * scale, fz = (z[i] - m2) * scale;
-        uint32_t cx = fx > 0.0 ? (fx < cells ? (uint32_t)fx : cmax) : 0u;   // NaN lands in cell 0
-        uint32_t cy = fy > 0.0 ? (fy < cells ? (uint32_t)fy : cmax) : 0u;
-        uint32_t cz = fz > 0.0 ? (fz < cells ? (uint32_t)fz : cmax) : 0u;
-        if (cx > cmax) cx = cmax;
-        if (cy > cmax) cy = cmax;
-        if (cz > cmax) cz = cmax;
-        keys[i] = hilbert3(cx, cy, cz, bits);
-        p4[i] = make_double4(x[i], y[i], z[i], 0.0);     // one 32-byte record per point: the gather below reads one sector, not three
-    }
-}
-
-__global__ void __launch_bounds__(256)
-gather_sorted_kernel(const uint32_t *__restrict__ sidx, int64_t n, const double4 *__restrict__ p4, double *__restrict__ sx,
-                     double *__restrict__ sy, double *__restrict__ sz, double4 *__restrict__ sp4)
-{
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        const double4 q = p4[sidx[i]];
-        sx[i] = q.x; sy[i] = q.y; sz[i] = q.z;
-        sp4[i] = make_double4(q.x, q.y, q.z, 0.0);
+    // two points per thread and step: six loads in flight per thread (HBM bound: 24 B read, 40 B written per point)
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += 2 * stride) {
+        const int64_t i2 = i + stride < n ? i + stride : i;
+        double px[2] = {x[i], x[i2]}, py[2] = {y[i], y[i2]}, pz[2] = {z[i], z[i2]};
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            if (u == 1 && i2 == i) break;
+            double fx = (px[u] - m0) * scale, fy = (py[u] - m1) * scale, fz = (pz[u] - m2) * scale;
+            uint32_t cx = fx > 0.0 ? (fx < cells ? (uint32_t)fx : cmax) : 0u;   // NaN lands in cell 0
+            uint32_t cy = fy > 0.0 ? (fy < cells ? (uint32_t)fy : cmax) : 0u;
+            uint32_t cz = fz > 0.0 ? (fz < cells ? (uint32_t)fz : cmax) : 0u;
+            if (cx > cmax) cx = cmax;
+            if (cy > cmax) cy = cmax;
+            if (cz > cmax) cz = cmax;
+            const int64_t j = u ? i2 : i;
+            keys[j] = hilbert3_lut(cx, cy, cz, bits, lut1, lut2);
+            p4[j] = make_double4(px[u], py[u], pz[u], 0.0);  // one 32-byte record per point: the gather below reads one sector, not three
+        }
     }
 }
 
@@ -122,6 +151,39 @@ __device__ __forceinline__ double warp_max_d(double v)
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) { double o = shfl_xor_d(v, d); v = o > v ? o : v; }
     return v;
+}
+
+// sorted copies of the points AND table 0 of the range tables: a warp holds the 32 points of one cell group, so their box
+// costs twelve shuffle reductions here instead of a kernel of its own that reads the sorted planes back (0.11 ms at 10 M)
+__global__ void __launch_bounds__(256)
+gather_sorted_kernel(const uint32_t *__restrict__ sidx, int64_t n, const double4 *__restrict__ p4, double *__restrict__ sx,
+                     double *__restrict__ sy, double *__restrict__ sz, double4 *__restrict__ sp4, const GridDesc g,
+                     double *__restrict__ box, float4 *__restrict__ boxq)
+{
+    const int lane = lane_id();
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const double INF = pos_inf();
+    for (int64_t grp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; grp < g.cnt[0]; grp += nw) {
+        const int64_t i = grp * 32 + lane;
+        double lo[3] = {INF, INF, INF}, hi[3] = {-INF, -INF, -INF};
+        if (i < n) {
+            const double4 q = p4[sidx[i]];
+            sx[i] = q.x; sy[i] = q.y; sz[i] = q.z;
+            sp4[i] = make_double4(q.x, q.y, q.z, 0.0);
+            lo[0] = hi[0] = q.x; lo[1] = hi[1] = q.y; lo[2] = hi[2] = q.z;
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { lo[k] = warp_min_d(lo[k]); hi[k] = warp_max_d(hi[k]); }
+        if (lane == 0) {
+            double *b = box + g.off[0];
+            const int64_t p = g.pitch[0];
+            b[grp] = lo[0]; b[p + grp] = lo[1]; b[2 * p + grp] = lo[2];
+            b[3 * p + grp] = hi[0]; b[4 * p + grp] = hi[1]; b[5 * p + grp] = hi[2];
+            float4 *bq = boxq + 2 * ((int64_t)g.qoff[0] + grp);
+            bq[0] = make_float4(__double2float_rd(lo[0]), __double2float_rd(lo[1]), __double2float_rd(lo[2]), __double2float_ru(hi[0]));
+            bq[1] = make_float4(__double2float_ru(hi[1]), __double2float_ru(hi[2]), 0.f, 0.f);
+        }
+    }
 }
 
 // one warp per entry of table `lvl`; children are points (lvl 0) or entries of table lvl-1
@@ -650,8 +712,6 @@ static int grid_build(o3dpp_ctx *c, GridDesc *gd)
     O3_TRY(radix_sort_pairs(c, c->s_keys0.as<uint64_t>(), c->s_keys1.as<uint64_t>(), c->s_vals0.as<uint32_t>(),
                             c->s_vals1.as<uint32_t>(), n, 3 * bits, &ks, &vs));
     CU_TRY(cudaMemcpyAsync(c->g_sidx.p, vs, (size_t)n * 4, cudaMemcpyDeviceToDevice, c->stream));
-    LAUNCH(c, gather_sorted_kernel, grid, 256, 0, c->g_sidx.as<uint32_t>(), n, c->g_p4.as<double4>(),
-           c->g_sx.as<double>(), c->g_sy.as<double>(), c->g_sz.as<double>(), c->g_sp4.as<double4>());
     // range tables
     int L = 0;
     int64_t cnt = (n + 31) / 32, off = 0;
@@ -675,7 +735,11 @@ static int grid_build(o3dpp_ctx *c, GridDesc *gd)
     gd->sp4 = c->g_sp4.as<double4>();
     gd->box = c->g_box.as<double>();
     gd->boxq = c->g_boxf.as<float4>();
-    for (int l = 0; l < L; ++l) {
+    // sorted copies + table 0 in one pass, then the upper tables
+    LAUNCH(c, gather_sorted_kernel, grid, 256, 0, c->g_sidx.as<uint32_t>(), n, c->g_p4.as<double4>(),
+           c->g_sx.as<double>(), c->g_sy.as<double>(), c->g_sz.as<double>(), c->g_sp4.as<double4>(), *gd,
+           c->g_box.as<double>(), c->g_boxf.as<float4>());
+    for (int l = 1; l < L; ++l) {
         int64_t warps = gd->cnt[l];
         int blocks = (int)((warps * 32 + 255) / 256);
         LAUNCH(c, box_level_kernel, blocks, 256, 0, *gd, l, c->g_box.as<double>(), c->g_boxf.as<float4>());

@@ -279,3 +279,13 @@ def test_gloo_world2_frames_and_slabs():
         p.join(30)
     assert all(r[1] == "ok" for r in res), res
     assert res[0][2] == res[1][2]                                 # identical cut planes on both ranks
+
+
+def test_hilbert_table_is_what_the_generator_writes():
+    """csrc/hilbert_lut.cuh (the curve of the neighbour grid as a state machine) is generated and checked against the
+    bit-twiddling Hilbert index for every bit count by tools/gen_hilbert_lut.py; the committed header must not drift"""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("gen_hilbert_lut", os.path.join(ROOT, "tools", "gen_hilbert_lut.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    assert mod.main(check_only=True)
