@@ -142,7 +142,7 @@ knn_finish_kernel(const GridDesc g, int K, double radius, KnnOut out, float *__r
 #pragma unroll
         for (int u = 0; u < KC_UNR; ++u) p[u] = j0 + u < K ? nb[(int64_t)(j0 + u) * out.nbr_pitch] : KNN_NONE;
 #pragma unroll
-        for (int u = 0; u < KC_UNR; ++u) v[u] = g.sp4[p[u] != KNN_NONE ? (int64_t)p[u] : q];     // unconditional: all in flight
+        for (int u = 0; u < KC_UNR; ++u) v[u] = ld_rec(g.sp4 + (p[u] != KNN_NONE ? (int64_t)p[u] : q));     // unconditional: all in flight
 #pragma unroll
         for (int u = 0; u < KC_UNR; ++u)
             if (p[u] != KNN_NONE && (MODE != 2 || dist2_rn(px, py, pz, v[u].x, v[u].y, v[u].z) < r2)) cu.add(v[u].x, v[u].y, v[u].z);

@@ -118,7 +118,7 @@ __device__ __forceinline__ int k2_range_query(const GridDesc &g, K2WarpMem &sm, 
 #pragma unroll
         for (int u = 0; u < K2_LUNR; ++u) {
             p[u] = s + u < np ? sm.leaf[s + u] * 32 + lane : n;
-            if (p[u] < n) c4[u] = g.sp4[p[u]];
+            if (p[u] < n) c4[u] = ld_rec(g.sp4 + p[u]);
         }
 #pragma unroll
         for (int u = 0; u < K2_LUNR; ++u) {

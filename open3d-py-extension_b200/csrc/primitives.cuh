@@ -199,9 +199,12 @@ static int compact_indices(o3dpp_ctx *c, Pred pred, int64_t n, int32_t *out, int
 #define RS_THREADS 256
 #define RS_WARPS 8
 #ifndef RS_ITEMS
-#define RS_ITEMS 8
+#define RS_ITEMS 6      // 1 536 keys per tile (4..12 measured at 10 M: within 3 %, 6 with six resident blocks best)
 #endif
 #define RS_TILE (RS_THREADS * RS_ITEMS)
+#ifndef RS_MINB
+#define RS_MINB 6
+#endif
 
 __global__ void __launch_bounds__(RS_THREADS)
 rs_hist_kernel(const uint64_t *__restrict__ keys, int64_t n, int shift, uint32_t dmask,
@@ -226,7 +229,7 @@ rs_hist_kernel(const uint64_t *__restrict__ keys, int64_t n, int shift, uint32_t
     thist[(int64_t)threadIdx.x * T + blockIdx.x] = h[threadIdx.x];
 }
 
-__global__ void __launch_bounds__(RS_THREADS)
+__global__ void __launch_bounds__(RS_THREADS, RS_MINB)
 rs_scatter_kernel(const uint64_t *__restrict__ kin, const uint32_t *__restrict__ vin,
                   uint64_t *__restrict__ kout, uint32_t *__restrict__ vout, int64_t n, int shift,
                   uint32_t dmask, const uint32_t *__restrict__ toff, int64_t T)
