@@ -30,6 +30,9 @@
 #ifndef KNN_NEAREST_FIRST
 #define KNN_NEAREST_FIRST 1
 #endif
+#ifndef KNN_BOXQ
+#define KNN_BOXQ 1
+#endif
 
 struct GridDesc {
     int64_t n;
@@ -472,7 +475,7 @@ struct Search {
         bool v = p < g.n;
         double d = pos_inf();
         double cx = 0, cy = 0, cz = 0;
-        if (v) { cx = g.sx[p]; cy = g.sy[p]; cz = g.sz[p]; d = dist2_rn(qx, qy, qz, cx, cy, cz); }
+        if (v) { const double4 c4 = ld_rec(g.sp4 + p); cx = c4.x; cy = c4.y; cz = c4.z; d = dist2_rn(qx, qy, qz, cx, cy, cz); }
         if (MODE == 1) {
             if (v && d < r2) cum.add(cx, cy, cz);
             return;
@@ -492,14 +495,28 @@ struct Search {
         }
     }
 
+    // lower bound of the squared distance from the query to box c of table lvl.  KNN_BOXQ: from the FP32 record (two loads,
+    // FP32 arithmetic rounded down, boxes rounded outwards), never above the FP64 value, so nothing that matters is pruned
     __device__ __forceinline__ double box_lb(int lvl, int64_t c)
     {
+#if KNN_BOXQ
+        const float4 *e = g.boxq + 2 * (g.qoff[lvl] + (int)c);
+        const float4 a = e[0];
+        const float2 b = *(const float2 *)(e + 1);
+        const float qxl = __double2float_rd(qx), qxh = __double2float_ru(qx), qyl = __double2float_rd(qy), qyh = __double2float_ru(qy),
+                    qzl = __double2float_rd(qz), qzh = __double2float_ru(qz);
+        float gx = fmaxf(fmaxf(__fsub_rd(a.x, qxh), __fsub_rd(qxl, a.w)), 0.f);
+        float gy = fmaxf(fmaxf(__fsub_rd(a.y, qyh), __fsub_rd(qyl, b.x)), 0.f);
+        float gz = fmaxf(fmaxf(__fsub_rd(a.z, qzh), __fsub_rd(qzl, b.y)), 0.f);
+        return (double)__fadd_rd(__fadd_rd(__fmul_rd(gx, gx), __fmul_rd(gy, gy)), __fmul_rd(gz, gz));
+#else
         const double *b = g.box + g.off[lvl];
         int64_t p = g.pitch[lvl];
         double gx = fmax(fmax(__dsub_rn(b[c], qx), __dsub_rn(qx, b[3 * p + c])), 0.0);
         double gy = fmax(fmax(__dsub_rn(b[p + c], qy), __dsub_rn(qy, b[4 * p + c])), 0.0);
         double gz = fmax(fmax(__dsub_rn(b[2 * p + c], qz), __dsub_rn(qz, b[5 * p + c])), 0.0);
         return __dadd_rn(__dadd_rn(__dmul_rn(gx, gx), __dmul_rn(gy, gy)), __dmul_rn(gz, gz));
+#endif
     }
 
     template <int LVL>
