@@ -101,6 +101,9 @@ __global__ void plane_model_kernel(const double *__restrict__ x, const double *_
 }
 
 // ---- scoring -----------------------------------------------------------------------------------
+// (Measured and not kept: an FP32 screen, t = a x + b y + c z + d in packed FP32 with a rigorous error margin, so that only
+// points within thr + margin take the FP64 evaluation.  7 % of the point x hypothesis pairs of the 10 M scan are inliers, but
+// 38 % of the 32-point warp steps touch one and a thread's four points share the branch: 1.13 ms against 0.97 ms.)
 #define SC_THREADS 256
 #define SC_PPT 4
 #define SC_HB 32   // hypotheses per block (blockIdx.y selects the chunk)
