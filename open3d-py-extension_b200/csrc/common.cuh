@@ -98,7 +98,7 @@ struct o3dpp_ctx {
     double timings[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     bool want_stats = false;              // O3DPP_STATS=1: search kernels count their work
     KnnTune tune;
-    unsigned long long stats[32] = {0};
+    unsigned long long stats[64] = {0};
 
     int64_t n = 0;
     Attr3 pts, nrm, col;

@@ -139,7 +139,7 @@ static int search_impl(o3dpp_ctx *c, int mode, int K, double radius, bool want_n
 
     if (c->want_stats) {
         out.stats = (unsigned long long *)(c->d_small.as<unsigned char>() + 56 * 1024);
-        CU_TRY(cudaMemsetAsync(out.stats, 0, 256, c->stream));
+        CU_TRY(cudaMemsetAsync(out.stats, 0, 512, c->stream));
     }
     GridDesc gd;
     c->kth_valid = false;
@@ -160,7 +160,7 @@ static int search_impl(o3dpp_ctx *c, int mode, int K, double radius, bool want_n
     O3_TRY(d2h(c, h_idx, c->g_nbr.p, (size_t)n * K * 4));
     O3_TRY(d2h(c, h_d2, c->g_nd2.p, (size_t)n * K * 8));
     O3_TRY(d2h(c, h_cnt, c->g_ncnt.p, (size_t)n * 4));
-    if (c->want_stats) O3_TRY(d2h(c, c->stats, out.stats, 256));
+    if (c->want_stats) O3_TRY(d2h(c, c->stats, out.stats, 512));
     CU_TRY(cudaStreamSynchronize(c->stream));
     float a = 0, b = 0;
     cudaEventElapsedTime(&a, c->ev[0], c->ev[1]);
@@ -187,6 +187,11 @@ static int search_impl(o3dpp_ctx *c, int mode, int K, double radius, bool want_n
                     t1, tg, tf, t2, t3, (long long)c->timings[4], (long long)c->timings[5], c->stats[25] / nw, c->stats[17] / nw, c->stats[18] / nw, c->stats[24] / nw,
                     c->stats[19] / nq, c->stats[20] / nq, c->stats[21] / nq, c->stats[22] / nq, c->stats[23] / nq,
                     c->stats[28] / nw, c->stats[26] / (nw - c->stats[28] + 1e-9) / 1e3, c->stats[27] / (c->stats[28] + 1e-9) / 1e3);
+            fprintf(stderr, "[o3dpp lane] by staged candidates (buckets of 96): groups");
+            for (int b = 0; b < 8; ++b) fprintf(stderr, " %llu", c->stats[40 + b]);
+            fprintf(stderr, " | lanes failing the radius test");
+            for (int b = 0; b < 8; ++b) fprintf(stderr, " %llu", c->stats[32 + b]);
+            fprintf(stderr, "\n");
         }
     }
     if (c->want_stats) {

@@ -599,6 +599,9 @@ knn_select_kernel(const GridDesc g, int K, double radius, float rho_scale, int m
                 atomicAdd(out.stats + 22, (unsigned long long)s4);
                 atomicAdd(out.stats + 23, (unsigned long long)s5);
                 atomicAdd(out.stats + 24, (unsigned long long)restage);
+                const int bk = min((have ? n_lo + n_hi : 32) / 96, 7);          // by staged candidates: where the radius test fails
+                atomicAdd(out.stats + 40 + bk, 1ull);
+                atomicAdd(out.stats + 32 + bk, (unsigned long long)s2);
             }
         }
     }
