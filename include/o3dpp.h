@@ -59,7 +59,11 @@ enum { O3DPP_ATTR_POINTS = 0, O3DPP_ATTR_NORMALS = 1, O3DPP_ATTR_COLORS = 2 };
  * (0 = built-in default; the same knobs are read once per context from the O3DPP_KNN_* environment variables). */
 enum {
     O3DPP_OPT_KEEP_NEIGHBORS = 1, O3DPP_OPT_STATS = 2, O3DPP_OPT_KNN_RHO = 3, O3DPP_OPT_KNN_GSPLIT = 4,
-    O3DPP_OPT_KNN_MAXSHRINK = 5, O3DPP_OPT_KNN_SHRINK = 6, O3DPP_OPT_KNN_BITS = 7, O3DPP_OPT_KNN_FORCE_LIST = 8
+    O3DPP_OPT_KNN_MAXSHRINK = 5, O3DPP_OPT_KNN_SHRINK = 6, O3DPP_OPT_KNN_BITS = 7, O3DPP_OPT_KNN_FORCE_LIST = 8,
+    /* value = m > 0: o3dpp_estimate_normals (knn <= 32, KNN or hybrid) answers only the FIRST m points of the cloud; every point stays
+     * a neighbour candidate, the normals of the others are left as they are.  0 = all points.  The second pass of a slab-sharded
+     * pure-KNN scan queries only the points whose k-th distance reaches across a cut (open3dpypro/sharding.py). */
+    O3DPP_OPT_QUERY_FIRST = 9
 };
 
 #define O3DPP_MAX_KNN 128
@@ -228,6 +232,9 @@ O3DPP_API int o3dpp_inlier_moments(o3dpp_ctx *ctx, const double *centroid3, doub
 /* per point, an upper bound of the squared distance to its k-th neighbour left by the last
  * o3dpp_estimate_normals (knn <= 32, KNN or hybrid): tells which queries near a slab cut need a wider halo */
 O3DPP_API int o3dpp_fetch_kth_bound(o3dpp_ctx *ctx, float *out);
+/* the same bounds written to n float32 of DEVICE memory (the sharded scan keeps its bookkeeping on the device: a 100 M-point
+ * slab would otherwise move 0.4 GB to the host and back) */
+O3DPP_API int o3dpp_fetch_kth_bound_dev(o3dpp_ctx *ctx, uintptr_t dev_out);
 
 /* measured FP64 FMA throughput of the device in TFLOP/s (2 flop per FMA): the roofline the scoring pass of
  * o3dpp_segment_plane (replaces the evaluation loop behind PointCloud.py:75-77) is reported against by bench.py */

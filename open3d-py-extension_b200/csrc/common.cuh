@@ -25,6 +25,7 @@ struct KnnTune {
     int bits = 0;           // curve cells per axis = 2^bits
     bool force_list = false;   // estimate_normals through the FP64 list kernel (A/B timing, parity cross-checks)
     bool keep = false;      // record the neighbour sets of every tier (o3dpp_fetch_neighbors)
+    int64_t query_first = 0;   // > 0: estimate_normals answers only the first query_first points (all points stay candidates)
 };
 
 static thread_local std::string g_last_error;

@@ -47,6 +47,7 @@ struct GridDesc {
     const float4 *boxq;               // the same boxes in FP32, rounded outwards (lo down, hi up): conservative culling;
                                       // two records per entry {lo.x lo.y lo.z hi.x} {hi.y hi.z - -}, entry e of table l at qoff[l] + e
     int qoff[KNN_MAX_LEVELS];
+    int64_t qfirst;                   // queries = the points with original index < qfirst (n: all); O3DPP_OPT_QUERY_FIRST
 };
 
 // ---- build -------------------------------------------------------------------------------
@@ -709,6 +710,7 @@ static int grid_build(o3dpp_ctx *c, GridDesc *gd)
     int64_t n = c->n;
     memset(gd, 0, sizeof *gd);
     gd->n = n;
+    gd->qfirst = (c->tune.query_first > 0 && c->tune.query_first < n) ? c->tune.query_first : n;
     O3_TRY(bounds_impl(c, nullptr, nullptr));   // d_small[0..5] = min, max
     int bits = 4;
     { int64_t m = 1; int lg = 0; while (m < n) { m <<= 1; ++lg; } bits = (lg + 1) / 2 + 1; }   // ~2 n^(1/2) cells per axis: measured as good as finer grids, one radix pass fewer at 10 M

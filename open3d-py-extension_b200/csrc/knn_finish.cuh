@@ -19,6 +19,7 @@
 #define KF_TCAP 1.0e30f
 #define KF_U 5.9604645e-8f /* 2^-24 */
 #define KNN_NONE 0xffffffffu
+#define KF_SKIP (-3.0e38f)   /* bound-buffer value of a point that is not a query (O3DPP_OPT_QUERY_FIRST): "answered", nothing to finish */
 
 #ifndef KL_GUARD
 #define KL_GUARD true   // order-sensitivity guard of the covariance (kf_store_normal); false only for A/B timing
@@ -129,7 +130,7 @@ knn_finish_kernel(const GridDesc g, int K, double radius, KnnOut out, float *__r
     const int64_t q = (int64_t)blockIdx.x * 128 + threadIdx.x;
     if (q >= g.n) return;
     const float cap = capbuf[q];
-    if (!(cap < 0.0f)) return;
+    if (!(cap < 0.0f) || cap <= KF_SKIP) return;
     const double r2 = __dmul_rn(radius, radius);
     double px = 0, py = 0, pz = 0;
     if (MODE == 2) { const double4 me = g.sp4[q]; px = me.x; py = me.y; pz = me.z; }

@@ -216,14 +216,14 @@ __global__ void kth_scatter_kernel(const float *__restrict__ capbuf, const uint3
     }
 }
 
-static int fetch_kth_impl(o3dpp_ctx *c, float *host)
+static int fetch_kth_impl(o3dpp_ctx *c, float *host, float *dev = nullptr)
 {
     if (!c->kth_valid) return set_err(O3DPP_E_STATE, "no k-th distance bounds: run o3dpp_estimate_normals (knn <= 32, KNN or hybrid) first");
     int64_t n = c->n;
     O3_TRY(c->g_nd2.ensure((size_t)n * 4 + 64));
-    LAUNCH(c, kth_scatter_kernel, grid_for(c, n, 256, 16), 256, 0, c->g_ncnt.as<float>(), c->g_sidx.as<uint32_t>(), n, c->g_nd2.as<float>());
+    LAUNCH(c, kth_scatter_kernel, grid_for(c, n, 256, 16), 256, 0, c->g_ncnt.as<float>(), c->g_sidx.as<uint32_t>(), n, dev ? dev : c->g_nd2.as<float>());
     O3_TRY(check_launch("kth_scatter"));
-    O3_TRY(d2h(c, host, c->g_nd2.p, (size_t)n * 4));
+    if (!dev) O3_TRY(d2h(c, host, c->g_nd2.p, (size_t)n * 4));
     CU_TRY(cudaStreamSynchronize(c->stream));
     return 0;
 }

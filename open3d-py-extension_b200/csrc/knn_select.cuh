@@ -166,6 +166,10 @@ knn_groups_kernel(const GridDesc g, double radius, float rho_scale, int max_shri
     const int lane = lane_id(), w = threadIdx.x >> 5;
     const int64_t leaf_id = (int64_t)blockIdx.x * KA_WARPS + w;
     if (leaf_id >= g.cnt[0]) return;
+    if (g.qfirst < g.n) {                        // O3DPP_OPT_QUERY_FIRST: a group none of whose points is a query needs no list
+        const int64_t p = leaf_id * 32 + lane;
+        if (!__any_sync(FULL, p < g.n && (int64_t)g.sidx[p] < g.qfirst)) return;
+    }
     KsHome h;
     ks_home<MODE>(g, leaf_id, radius, rho_scale, h);
     const unsigned lt = (1u << lane) - 1u;
@@ -275,6 +279,14 @@ knn_select_kernel(const GridDesc g, int K, double radius, float rho_scale, int m
     const int64_t mypos = base + lane;
     const bool valid = lane < nq;
     double px = 0, py = 0, pz = 0;
+    bool want = valid;                           // O3DPP_OPT_QUERY_FIRST: only the points with original index < qfirst are queries
+    if (g.qfirst < g.n) {
+        want = valid && (int64_t)g.sidx[mypos] < g.qfirst;
+        if (!__any_sync(FULL, want)) {           // nothing to answer here (both warps of a pair agree): the whole block leaves
+            if (w == 0 && valid) capbuf[mypos] = KF_SKIP;
+            return;
+        }
+    }
     if (valid) { px = g.sx[mypos]; py = g.sy[mypos]; pz = g.sz[mypos]; }
     KsHome h;
     ks_home<MODE>(g, leaf_id, radius, rho_scale, h);
@@ -582,8 +594,8 @@ knn_select_kernel(const GridDesc g, int K, double radius, float rho_scale, int m
     }
     if (w == 0) {
         if (valid) {
-            capbuf[mypos] = ok ? -fmaxf(capf, 1e-30f) : capf;   // negative = answered, magnitude bounds the k-th d2
-            if (out.keep && ok) out.tier[mypos] = 1;
+            capbuf[mypos] = !want ? KF_SKIP : ok ? -fmaxf(capf, 1e-30f) : capf;   // negative = answered, magnitude bounds the k-th d2
+            if (out.keep && ok && want) out.tier[mypos] = 1;
         }
         if (out.stats) {
             const unsigned s1 = __reduce_add_sync(FULL, (unsigned)(valid && why == 1)), s2 = __reduce_add_sync(FULL, (unsigned)(valid && why == 2)),

@@ -131,6 +131,7 @@ O3DPP_API int o3dpp_set_option(o3dpp_ctx *c, int option, double value)
     case O3DPP_OPT_KNN_SHRINK: c->tune.shrink = (float)value; break;
     case O3DPP_OPT_KNN_BITS: c->tune.bits = (int)value; break;
     case O3DPP_OPT_KNN_FORCE_LIST: c->tune.force_list = value != 0.0; break;
+    case O3DPP_OPT_QUERY_FIRST: c->tune.query_first = value > 0.0 ? (int64_t)value : 0; break;
     default: return set_err(O3DPP_E_ARG, "unknown option");
     }
     return 0;
@@ -407,6 +408,12 @@ O3DPP_API int o3dpp_fetch_kth_bound(o3dpp_ctx *c, float *out)
     CTX_CHECK(c);
     if (!out) return set_err(O3DPP_E_ARG, "null argument");
     return fetch_kth_impl(c, out);
+}
+O3DPP_API int o3dpp_fetch_kth_bound_dev(o3dpp_ctx *c, uintptr_t dev_out)
+{
+    CTX_CHECK(c);
+    if (!dev_out) return set_err(O3DPP_E_ARG, "null argument");
+    return fetch_kth_impl(c, nullptr, (float *)dev_out);
 }
 
 /* ---- callers either side of the path ------------------------------------------------ */

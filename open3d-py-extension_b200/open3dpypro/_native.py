@@ -20,7 +20,7 @@ SAMPLER_PHILOX, SAMPLER_MT19937, SAMPLER_GIVEN = 0, 1, 2
 F32, F64 = 0, 1
 MAX_KNN = 128
 (OPT_KEEP_NEIGHBORS, OPT_STATS, OPT_KNN_RHO, OPT_KNN_GSPLIT, OPT_KNN_MAXSHRINK, OPT_KNN_SHRINK, OPT_KNN_BITS,
- OPT_KNN_FORCE_LIST) = range(1, 9)
+ OPT_KNN_FORCE_LIST, OPT_QUERY_FIRST) = range(1, 10)
 
 # every symbol include/o3dpp.h declares (tests check the library exports all of them)
 SYMBOLS = [
@@ -34,7 +34,7 @@ SYMBOLS = [
     "o3dpp_plane_inliers", "o3dpp_inlier_moments", "o3dpp_fetch_kth_bound", "o3dpp_knn_mean_distance", "o3dpp_zsplat", "o3dpp_download_async",
     "o3dpp_set_option", "o3dpp_fetch_neighbors", "o3dpp_voxel_bounded", "o3dpp_download_as", "o3dpp_download_rows6",
     "o3dpp_host_register", "o3dpp_host_unregister", "o3dpp_fp64_peak", "o3dpp_transform_points",
-    "o3dpp_bounds_static",
+    "o3dpp_bounds_static", "o3dpp_fetch_kth_bound_dev",
 ]
 
 _lib = None
@@ -442,6 +442,11 @@ class Context:
         if out.size:
             _check(lib().o3dpp_fetch_kth_bound(self._h, _ptr(out)))
         return out
+
+    def kth_bound_dev(self, dev_ptr):
+        """the same bounds into size() float32 of device memory"""
+        if self.size():
+            _check(lib().o3dpp_fetch_kth_bound_dev(self._h, C.c_size_t(dev_ptr)))
 
 
 _contexts = {}

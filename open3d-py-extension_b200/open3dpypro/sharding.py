@@ -240,13 +240,19 @@ def slab_estimate_normals(ctx, owned: np.ndarray, axis: int, cuts: Sequence[floa
             halo = exchange_halo(owned, axis, cuts, rank, world, halo_w, group)
             info.update(halo_width=halo_w, halo_points=int(len(halo)), passes=2)
             if unsafe.any():
+                # the unsafe queries first: only they are queried (O3DPP_OPT_QUERY_FIRST), the rest of the strips are candidates
                 near = to_cut <= 2.0 * halo_w
-                ctx.upload(nat.ATTR_POINTS, np.concatenate([owned[near], halo], 0))
+                m = int(unsafe.sum())
+                ctx.upload(nat.ATTR_POINTS, np.concatenate([owned[unsafe], owned[near & ~unsafe], halo], 0))
                 ctx.drop(nat.ATTR_NORMALS)
-                ctx.estimate_normals(mode, knn, radius)
-                n2 = _download_normals(ctx, int(near.sum()))
-                nrm[unsafe] = n2[(np.cumsum(near) - 1)[unsafe]]
+                ctx.set_option(nat.OPT_QUERY_FIRST, m)
+                try:
+                    ctx.estimate_normals(mode, knn, radius)
+                finally:
+                    ctx.set_option(nat.OPT_QUERY_FIRST, 0)
+                nrm[unsafe] = _download_normals(ctx, m)
                 info["second_pass_points"] = int(near.sum()) + int(len(halo))
+                info["second_pass_queries"] = m
             ctx.upload(nat.ATTR_POINTS, owned)          # the context is left holding the owned points (slab_segment_plane)
             ctx.drop(nat.ATTR_NORMALS)
             return nrm, info
@@ -632,7 +638,11 @@ def dev_slab_estimate_normals(ctx, owned, axis: int, cuts, rank: int, world: int
         if n_own:
             run(owned)
             nrm = fetch(n_own)
-            r = torch.from_numpy(ctx.kth_bound()).to(owned.device).double().sqrt_() * (1.0 + 1e-6)
+            kb = torch.empty(n_own, dtype=torch.float32, device=owned.device)
+            ctx.kth_bound_dev(kb.data_ptr())
+            ctx.synchronize()
+            r = kb.double().sqrt_() * (1.0 + 1e-6)
+            del kb
             x = owned[:, axis]
             to_cut = torch.minimum(x - float(cuts[rank]), float(cuts[rank + 1]) - x)
             unsafe = r > to_cut
@@ -643,12 +653,20 @@ def dev_slab_estimate_normals(ctx, owned, axis: int, cuts, rank: int, world: int
             halo = exchange(halo_w)
             info["passes"] = 2
             if unsafe is not None and bool(unsafe.any()):
+                # the unsafe queries first: only they are queried (O3DPP_OPT_QUERY_FIRST), the rest of the strips are candidates
                 near = to_cut <= 2.0 * halo_w
-                n_near = int(near.sum())
-                run(torch.cat([owned[near], halo], 0))
-                n2 = fetch(n_near)
-                nrm[unsafe] = n2[(torch.cumsum(near.long(), 0) - 1)[unsafe]]
-                info["second_pass_points"] = n_near + int(len(halo))
+                first = owned[unsafe]
+                m = int(len(first))
+                rest = owned[near & ~unsafe]
+                ctx.set_option(nat.OPT_QUERY_FIRST, m)
+                try:
+                    run(torch.cat([first, rest, halo], 0))
+                finally:
+                    ctx.set_option(nat.OPT_QUERY_FIRST, 0)
+                nrm[unsafe] = fetch(m)
+                info["second_pass_points"] = m + int(len(rest)) + int(len(halo))
+                info["second_pass_queries"] = m
+                del first, rest
             if n_own:
                 _sync_torch()
                 ctx.upload_dev(nat.ATTR_POINTS, owned.contiguous().data_ptr(), n_own, nat.F64)   # left holding the owned points

@@ -120,3 +120,30 @@ def test_sets_c3_sample(kctx, orc, mode, radius):
     qi = np.random.default_rng(5).choice(len(scan), 2000, replace=False)
     counts = _check_sets(kctx, orc, scan, mode=mode, radius=radius, queries=qi)
     assert counts[1] > 1500          # most of the sample is answered by the certified FP32 selection
+
+
+@pytest.mark.parametrize("mode,radius", [(0, 0.0), (2, 0.5)])
+def test_query_first_answers_only_the_first_points(kctx, orc, mode, radius):
+    """O3DPP_OPT_QUERY_FIRST = m (second pass of the slab-sharded pure-KNN scan): the first m points get exactly the
+    normals and neighbour sets of the full call, whichever tier answers them; the others are not queried"""
+    pts = lidar_like(150_000, 81)
+    kctx.upload(nat.ATTR_POINTS, pts)
+    kctx.drop(nat.ATTR_NORMALS)
+    kctx.estimate_normals(mode, K, radius)
+    full = np.empty((len(pts), 3))
+    kctx.download(nat.ATTR_NORMALS, full)
+    try:
+        for m in (1, 777, 40_000, len(pts)):
+            kctx.drop(nat.ATTR_NORMALS)
+            kctx.set_option(nat.OPT_QUERY_FIRST, m)
+            kctx.estimate_normals(mode, K, radius)
+            got = np.empty((len(pts), 3))
+            kctx.download(nat.ATTR_NORMALS, got)
+            assert np.array_equal(got[:m], full[:m]), m
+            qi = np.unique(np.random.default_rng(m).integers(0, m, min(m, 1500)))
+            idx, cnt, tier = kctx.fetch_neighbors(K, qi)
+            e, ecnt = _expected_sets(orc, pts, K, mode, radius, qi)
+            assert np.array_equal(cnt, ecnt) and np.array_equal(idx, e)
+            assert ((tier >= 1) & (tier <= 3)).all()
+    finally:
+        kctx.set_option(nat.OPT_QUERY_FIRST, 0)
