@@ -376,6 +376,8 @@ def run_c5(ctx, nat, rank, world, local, dist, barrier, total):
         out[name] = {"normals_ms": tn, "segment_ms": ts_, "mpoints_per_s": total / ((tn + ts_) * 1e-3) / 1e6, "max_halo_points": int(halo),
                      "max_halo_bytes_received": int(hb), "halo_exchange_ms": ex, "halo_width": info["halo_width"], "passes": info["passes"],
                      "n_inliers": pinfo["n_inliers"], "max_owned_points": int(_max_over_ranks([len(owned)], dist, local)[0]),
+                     "max_second_pass_points": int(_max_over_ranks([info.get("second_pass_points", 0)], dist, local)[0]),
+                     "max_second_pass_queries": int(_max_over_ranks([info.get("second_pass_queries", 0)], dist, local)[0]),
                      "collectives": "all_to_all_single (halo) + all-reduce of 3H sampled points, H counts + H error sums per 64-hypothesis batch, centroid, 6 moments"}
     return out
 
@@ -510,11 +512,12 @@ def main():
             plane, inl = c.segment_plane(THR, RANSAC_N, ITERS, seed=1, inliers_out=hx.array)   # D2H inliers + plane
         else:                                          # several in flight: the normals leave while the NEXT scan computes
             c.synchronize()
-            with token:
+            with token:                                # the token covers the kernels only: the results leave after it is passed on
                 c.drop(nat.ATTR_NORMALS)
                 c.estimate_normals(nat.SEARCH_KNN, KNN, 0.0)
-                plane, inl = c.segment_plane(THR, RANSAC_N, ITERS, seed=1, inliers_out=hx.array)
-                c.download_async(nat.ATTR_NORMALS, ho.array)
+                plane, _ = c.segment_plane(THR, RANSAC_N, ITERS, seed=1, fetch_inliers=False)
+            c.download_async(nat.ATTR_NORMALS, ho.array)   # D2H 24 B/point on the copy stream
+            inl = c.fetch_inliers_into(hx.array)           # D2H inlier list
         c.synchronize()                                # normals complete on the host
         return plane, inl
 

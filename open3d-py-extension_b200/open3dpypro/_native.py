@@ -140,6 +140,7 @@ class Context:
         self.device = device
         self._pid = os.getpid()
         self.generation = 0
+        self.n_inliers = 0
         _check(lib().o3dpp_create(C.c_int(device), C.byref(self._h)))
 
     def close(self):
@@ -342,6 +343,7 @@ class Context:
                                          C.c_double(probability), C.c_int(sampler), C.c_uint64(seed), _ptr(s),
                                          _ptr(plane), C.byref(m), _ptr(best), C.byref(bi), _ptr(counts), _ptr(errs)))
         inl = None
+        self.n_inliers = m.value                     # for fetch_inliers_into after a call with fetch_inliers=False
         if fetch_inliers:
             if inliers_out is not None:
                 if inliers_out.dtype != np.int32 or not inliers_out.flags.c_contiguous or inliers_out.size < m.value:
@@ -402,6 +404,17 @@ class Context:
         s3 = np.zeros(3)
         _check(lib().o3dpp_plane_inliers(self._h, _ptr(plane), C.c_double(distance_threshold), C.c_int64(n_use), C.byref(m), _ptr(s3)))
         return m.value, s3
+
+    def fetch_inliers_into(self, out):
+        """the inlier list of the last segment_plane (fetch_inliers=False) into a caller-owned int32 buffer (e.g. page-locked);
+        returns the view of its first n_inliers entries"""
+        m = self.n_inliers
+        if out.dtype != np.int32 or not out.flags.c_contiguous or out.size < m:
+            raise ValueError("out must be a contiguous int32 array with room for every inlier")
+        inl = out.reshape(-1)[:m]
+        if m:
+            _check(lib().o3dpp_fetch_inliers(self._h, _ptr(inl)))
+        return inl
 
     def fetch_inlier_list(self, m):
         inl = np.empty(int(m), np.int32)
