@@ -110,7 +110,8 @@ __device__ __forceinline__ uint64_t hilbert3_lut(uint32_t x, uint32_t y, uint32_
 
 __global__ void __launch_bounds__(256)
 curve_key_kernel(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
-                  int64_t n, const double *__restrict__ mnmx, int bits, uint64_t *__restrict__ keys, double4 *__restrict__ p4)
+                  int64_t n, const double *__restrict__ mnmx, int bits, int pack /* index bits below the key, 0 = none */,
+                  uint64_t *__restrict__ keys, double4 *__restrict__ p4)
 {
     __shared__ unsigned short lut2[HILBERT_STATES * 64];
     __shared__ unsigned char lut1[8];
@@ -138,7 +139,8 @@ curve_key_kernel(const double *__restrict__ x, const double *__restrict__ y, con
             if (cy > cmax) cy = cmax;
             if (cz > cmax) cz = cmax;
             const int64_t j = u ? i2 : i;
-            keys[j] = hilbert3_lut(cx, cy, cz, bits, lut1, lut2);
+            const uint64_t hk = hilbert3_lut(cx, cy, cz, bits, lut1, lut2);
+            keys[j] = pack ? (hk << pack) | (uint64_t)j : hk;
             p4[j] = make_double4(px[u], py[u], pz[u], 0.0);  // one 32-byte record per point: the gather below reads one sector, not three
         }
     }
@@ -725,12 +727,20 @@ static int grid_build(o3dpp_ctx *c, GridDesc *gd)
     O3_TRY(c->g_sp4.ensure(nn * 32));
     O3_TRY(c->g_p4.ensure(nn * 32));
     int grid = grid_for(c, n, 256, 16);
-    LAUNCH(c, curve_key_kernel, grid, 256, 0, c->pts.x(), c->pts.y(), c->pts.z(), n, c->d_small.as<double>(), bits,
+    // up to 16.7 M points with a key of at most 40 bits: the original index rides in the low 24 bits of the key and the sort
+    // moves 8 bytes per element and pass instead of 12
+    const int pack = (n <= ((int64_t)1 << RS_PACK_BITS) && 3 * bits + RS_PACK_BITS <= 64) ? RS_PACK_BITS : 0;
+    LAUNCH(c, curve_key_kernel, grid, 256, 0, c->pts.x(), c->pts.y(), c->pts.z(), n, c->d_small.as<double>(), bits, pack,
            c->s_keys0.as<uint64_t>(), c->g_p4.as<double4>());
     uint64_t *ks; uint32_t *vs;
-    O3_TRY(radix_sort_pairs(c, c->s_keys0.as<uint64_t>(), c->s_keys1.as<uint64_t>(), c->s_vals0.as<uint32_t>(),
-                            c->s_vals1.as<uint32_t>(), n, 3 * bits, &ks, &vs));
-    CU_TRY(cudaMemcpyAsync(c->g_sidx.p, vs, (size_t)n * 4, cudaMemcpyDeviceToDevice, c->stream));
+    if (pack) {
+        O3_TRY(radix_sort_packed(c, c->s_keys0.as<uint64_t>(), c->s_keys1.as<uint64_t>(), n, pack, 3 * bits, &ks));
+        LAUNCH(c, unpack_index_kernel, grid, 256, 0, ks, n, c->g_sidx.as<uint32_t>());
+    } else {
+        O3_TRY(radix_sort_pairs(c, c->s_keys0.as<uint64_t>(), c->s_keys1.as<uint64_t>(), c->s_vals0.as<uint32_t>(),
+                                c->s_vals1.as<uint32_t>(), n, 3 * bits, &ks, &vs));
+        CU_TRY(cudaMemcpyAsync(c->g_sidx.p, vs, (size_t)n * 4, cudaMemcpyDeviceToDevice, c->stream));
+    }
     // range tables
     int L = 0;
     int64_t cnt = (n + 31) / 32, off = 0;

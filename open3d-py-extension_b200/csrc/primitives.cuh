@@ -229,6 +229,7 @@ rs_hist_kernel(const uint64_t *__restrict__ keys, int64_t n, int shift, uint32_t
     thist[(int64_t)threadIdx.x * T + blockIdx.x] = h[threadIdx.x];
 }
 
+template <bool VALS>        // false: keys only (the payload rides in the key bits below the sorted range)
 __global__ void __launch_bounds__(RS_THREADS, RS_MINB)
 rs_scatter_kernel(const uint64_t *__restrict__ kin, const uint32_t *__restrict__ vin,
                   uint64_t *__restrict__ kout, uint32_t *__restrict__ vout, int64_t n, int shift,
@@ -238,7 +239,7 @@ rs_scatter_kernel(const uint64_t *__restrict__ kin, const uint32_t *__restrict__
     __shared__ uint32_t dbase[256];
     __shared__ uint32_t sh[34];
     __shared__ uint64_t skey[RS_TILE];
-    __shared__ uint32_t sval[RS_TILE];
+    __shared__ uint32_t sval[VALS ? RS_TILE : 1];
     const int lane = lane_id(), w = threadIdx.x >> 5;
     const int64_t tbase = (int64_t)blockIdx.x * RS_TILE;
     for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&wcnt[0][0])[i] = 0;
@@ -252,7 +253,7 @@ rs_scatter_kernel(const uint64_t *__restrict__ kin, const uint32_t *__restrict__
         int64_t j = tbase + w * (RS_ITEMS * 32) + r * 32 + lane;
         bool valid = j < n;
         key[r] = valid ? kin[j] : 0ull;
-        val[r] = valid ? (vin ? vin[j] : (uint32_t)j) : 0u;
+        val[r] = !VALS ? 0u : valid ? (vin ? vin[j] : (uint32_t)j) : 0u;
         uint32_t d = (uint32_t)(key[r] >> shift) & dmask;
         uint32_t deff = valid ? d : (256u + lane);
         uint32_t peers = __match_any_sync(FULL, deff);
@@ -289,7 +290,7 @@ rs_scatter_kernel(const uint64_t *__restrict__ kin, const uint32_t *__restrict__
             uint32_t d = (uint32_t)(key[r] >> shift) & dmask;
             uint32_t pos = dbase[d] + wcnt[w][d] + rk[r];
             skey[pos] = key[r];
-            sval[pos] = val[r];
+            if (VALS) sval[pos] = val[r];
         }
     }
     __syncthreads();
@@ -298,7 +299,7 @@ rs_scatter_kernel(const uint64_t *__restrict__ kin, const uint32_t *__restrict__
         uint32_t d = (uint32_t)(k >> shift) & dmask;
         int64_t g = (int64_t)toff[(int64_t)d * T + blockIdx.x] + (i - dbase[d]);
         kout[g] = k;
-        vout[g] = sval[i];
+        if (VALS) vout[g] = sval[i];
     }
 }
 
@@ -321,7 +322,7 @@ static int radix_sort_pairs(o3dpp_ctx *c, uint64_t *keys0, uint64_t *keys1, uint
         uint32_t dmask = (1u << bits) - 1u;
         LAUNCH(c, rs_hist_kernel, (int)T, RS_THREADS, 0, kin, n, shift, dmask, thist, T);
         O3_TRY(exclusive_scan_u32(c, thist, thist, T * 256));
-        LAUNCH(c, rs_scatter_kernel, (int)T, RS_THREADS, 0, kin, vin, kout, vout, n, shift, dmask, thist, T);
+        LAUNCH(c, rs_scatter_kernel<true>, (int)T, RS_THREADS, 0, kin, vin, kout, vout, n, shift, dmask, thist, T);
         O3_TRY(check_launch("radix pass"));
         uint64_t *tk = kin; kin = kout; kout = tk;
         vin = vout;
@@ -330,4 +331,34 @@ static int radix_sort_pairs(o3dpp_ctx *c, uint64_t *keys0, uint64_t *keys1, uint
     *keys_sorted = kin;
     *vals_sorted = vin;
     return 0;
+}
+
+// Keys only, sorted by the bits [shift0, shift0 + nbits): the caller packs its payload (the original index) into the bits
+// below shift0, so a pass moves 8 bytes per element instead of 12 and the result is the stable order of the pair sort.
+// RS_PACK_BITS = 24 index bits: clouds of up to 16.7 M points whose key needs at most 40 bits.
+#define RS_PACK_BITS 24
+static int radix_sort_packed(o3dpp_ctx *c, uint64_t *keys0, uint64_t *keys1, int64_t n, int shift0, int nbits, uint64_t **keys_sorted)
+{
+    int64_t T = (n + RS_TILE - 1) / RS_TILE;
+    if (T < 1) T = 1;
+    O3_TRY(c->s_hist.ensure((size_t)T * 256 * sizeof(uint32_t) + 1024));
+    uint32_t *thist = c->s_hist.as<uint32_t>();
+    uint64_t *kin = keys0, *kout = keys1;
+    for (int shift = 0; shift < nbits; shift += 8) {
+        int bits = nbits - shift < 8 ? nbits - shift : 8;
+        uint32_t dmask = (1u << bits) - 1u;
+        LAUNCH(c, rs_hist_kernel, (int)T, RS_THREADS, 0, kin, n, shift0 + shift, dmask, thist, T);
+        O3_TRY(exclusive_scan_u32(c, thist, thist, T * 256));
+        LAUNCH(c, rs_scatter_kernel<false>, (int)T, RS_THREADS, 0, kin, nullptr, kout, nullptr, n, shift0 + shift, dmask, thist, T);
+        O3_TRY(check_launch("radix pass (packed)"));
+        uint64_t *tk = kin; kin = kout; kout = tk;
+    }
+    *keys_sorted = kin;
+    return 0;
+}
+
+__global__ void unpack_index_kernel(const uint64_t *__restrict__ packed, int64_t n, uint32_t *__restrict__ idx)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        idx[i] = (uint32_t)packed[i] & ((1u << RS_PACK_BITS) - 1u);
 }

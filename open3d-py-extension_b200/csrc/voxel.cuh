@@ -17,7 +17,7 @@ struct VoxOrigin {                   // grid origin (min_bound) and the smallest
 
 // one point: its 32-byte record (position + octant) and its key
 __device__ __forceinline__ void voxel_key_one(double px, double py, double pz, int64_t i, const VoxOrigin &og, double voxel_size,
-                                              const VoxPack &pk, int wide, uint64_t *__restrict__ key_lo,
+                                              const VoxPack &pk, int wide, int pack, uint64_t *__restrict__ key_lo,
                                               uint32_t *__restrict__ key_ix, double4 *__restrict__ p4)
 {
     double r0 = __ddiv_rn(__dsub_rn(px, og.o[0]), voxel_size);
@@ -35,7 +35,8 @@ __device__ __forceinline__ void voxel_key_one(double px, double py, double pz, i
         key_lo[i] = (iy << pk.bz) | iz;
         key_ix[i] = (uint32_t)ix;
     } else {
-        key_lo[i] = (ix << (pk.by + pk.bz)) | (iy << pk.bz) | iz;
+        const uint64_t k = (ix << (pk.by + pk.bz)) | (iy << pk.bz) | iz;
+        key_lo[i] = pack ? (k << pack) | (uint64_t)i : k;          // packed: the original index rides below the key (radix_sort_packed)
     }
 }
 
@@ -43,7 +44,7 @@ __device__ __forceinline__ void voxel_key_one(double px, double py, double pz, i
 // (one point per step left the kernel latency bound at 62 % of the copy rate, ncu r02y)
 __global__ void __launch_bounds__(256)
 voxel_key_kernel(const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
-                 int64_t n, const VoxOrigin og, double voxel_size, VoxPack pk, int wide,
+                 int64_t n, const VoxOrigin og, double voxel_size, VoxPack pk, int wide, int pack,
                  uint64_t *__restrict__ key_lo, uint32_t *__restrict__ key_ix, double4 *__restrict__ p4)
 {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -52,8 +53,8 @@ voxel_key_kernel(const double *__restrict__ x, const double *__restrict__ y, con
         const bool two = i2 < n;
         const double ax = x[i], ay = y[i], az = z[i];
         const double bx = two ? x[i2] : 0.0, by = two ? y[i2] : 0.0, bz = two ? z[i2] : 0.0;
-        voxel_key_one(ax, ay, az, i, og, voxel_size, pk, wide, key_lo, key_ix, p4);
-        if (two) voxel_key_one(bx, by, bz, i2, og, voxel_size, pk, wide, key_lo, key_ix, p4);
+        voxel_key_one(ax, ay, az, i, og, voxel_size, pk, wide, pack, key_lo, key_ix, p4);
+        if (two) voxel_key_one(bx, by, bz, i2, og, voxel_size, pk, wide, pack, key_lo, key_ix, p4);
     }
 }
 
@@ -66,7 +67,8 @@ __global__ void gather_u32_as_key_kernel(const uint32_t *__restrict__ src, const
 
 struct HeadPred {  // sorted position j starts a row
     const uint64_t *keys;
-    __device__ bool operator()(int64_t j) const { return j == 0 || keys[j] != keys[j - 1]; }
+    int shift;          // packed keys: the index bits below the key are not part of it
+    __device__ bool operator()(int64_t j) const { return j == 0 || (keys[j] >> shift) != (keys[j - 1] >> shift); }
 };
 struct HeadPredWide {
     const uint64_t *key_lo;   // per ORIGINAL point
@@ -189,17 +191,23 @@ static int voxel_impl(o3dpp_ctx *c, double voxel_size, const double *min3, const
         key_ix = wide_ix.as<uint32_t>();
     }
     int grid = grid_for(c, n, 256, 16);
+    const int pack = (!wide && n <= ((int64_t)1 << RS_PACK_BITS) && pk.bx + pk.by + pk.bz + RS_PACK_BITS <= 64) ? RS_PACK_BITS : 0;
     LAUNCH(c, voxel_key_kernel, grid, 256, 0, c->pts.x(), c->pts.y(), c->pts.z(), n, og,
-           voxel_size, pk, wide, key_lo, key_ix, c->g_p4.as<double4>());
+           voxel_size, pk, wide, pack, key_lo, key_ix, c->g_p4.as<double4>());
     O3_TRY(check_launch("voxel_key"));
     uint64_t *ks = nullptr;
     uint32_t *vs = nullptr;
     int64_t V = 0;
     int32_t *heads = c->v_seg.as<int32_t>();
-    if (!wide) {
+    if (pack) {
+        O3_TRY(radix_sort_packed(c, c->s_keys0.as<uint64_t>(), c->s_keys1.as<uint64_t>(), n, pack, pk.bx + pk.by + pk.bz, &ks));
+        HeadPred hp{ks, pack};
+        O3_TRY(compact_indices(c, hp, n, heads, &V));
+        LAUNCH(c, unpack_index_kernel, grid, 256, 0, ks, n, c->v_order.as<uint32_t>());
+    } else if (!wide) {
         O3_TRY(radix_sort_pairs(c, c->s_keys0.as<uint64_t>(), c->s_keys1.as<uint64_t>(), c->s_vals0.as<uint32_t>(),
                                 c->s_vals1.as<uint32_t>(), n, pk.bx + pk.by + pk.bz, &ks, &vs));
-        HeadPred hp{ks};
+        HeadPred hp{ks, 0};
         O3_TRY(compact_indices(c, hp, n, heads, &V));
     } else {
         // stage 1: (iy,iz) ; stage 2: ix, stable, payload carried over
@@ -214,7 +222,7 @@ static int voxel_impl(o3dpp_ctx *c, double voxel_size, const double *min3, const
         HeadPredWide hp{key_lo, key_ix, vs};
         O3_TRY(compact_indices(c, hp, n, heads, &V));
     }
-    CU_TRY(cudaMemcpyAsync(c->v_order.p, vs, (size_t)n * 4, cudaMemcpyDeviceToDevice, c->stream));
+    if (!pack) CU_TRY(cudaMemcpyAsync(c->v_order.p, vs, (size_t)n * 4, cudaMemcpyDeviceToDevice, c->stream));
     size_t vv = (size_t)V + 64;
     O3_TRY(c->v_rep.ensure(vv * 4)); O3_TRY(c->v_rep_asc.ensure(vv * 4)); O3_TRY(c->v_count.ensure(vv * 4));
     O3_TRY(c->v_centroid.ensure(vv * 24)); O3_TRY(c->v_normal.ensure(vv * 24)); O3_TRY(c->v_color.ensure(vv * 24));
