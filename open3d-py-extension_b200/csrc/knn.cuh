@@ -62,28 +62,11 @@ __device__ __forceinline__ uint64_t spread3(uint64_t v)
     return v;
 }
 
-// Hilbert index of a cell (Skilling's transpose algorithm), `bits` bits per axis.  Unlike the Morton
-// code, consecutive cells are always face neighbours, so 32 consecutive sorted points form a compact
-// blob: measured on the 1 M-point LiDAR-like scan, the number of cell groups within half a box
-// diagonal of a group drops from 124 (Morton) to 43 (tools/knn_leaf_study.py).
-__device__ __forceinline__ uint64_t hilbert3(uint32_t x, uint32_t y, uint32_t z, int bits)
-{
-    uint32_t X0 = x, X1 = y, X2 = z;
-    const uint32_t M = 1u << (bits - 1);
-    for (uint32_t Q = M; Q > 1u; Q >>= 1) {
-        const uint32_t P = Q - 1u;
-        if (X0 & Q) X0 ^= P;                                    // i = 0: the swap with itself is a no-op
-        if (X1 & Q) X0 ^= P; else { uint32_t t = (X0 ^ X1) & P; X0 ^= t; X1 ^= t; }
-        if (X2 & Q) X0 ^= P; else { uint32_t t = (X0 ^ X2) & P; X0 ^= t; X2 ^= t; }
-    }
-    X1 ^= X0; X2 ^= X1;
-    uint32_t t = 0;
-    for (uint32_t Q = M; Q > 1u; Q >>= 1) if (X2 & Q) t ^= Q - 1u;
-    X0 ^= t; X1 ^= t; X2 ^= t;
-    return (spread3(X0) << 2) | (spread3(X1) << 1) | spread3(X2);
-}
-
-// the same index through the generated state machine (hilbert_lut.cuh): Morton code, then two octants per table lookup.
+// Hilbert index of a cell, `bits` bits per axis (the curve of Skilling's transpose algorithm; tools/gen_hilbert_lut.py holds the
+// bit-twiddling form and checks the table against it).  Unlike the Morton code, consecutive cells are always face neighbours,
+// so 32 consecutive sorted points form a compact blob: measured on the 1 M-point LiDAR-like scan, the number of cell groups
+// within half a box diagonal of a group drops from 124 (Morton) to 43 (tools/knn_leaf_study.py).
+// The index comes from the generated state machine (hilbert_lut.cuh): Morton code, then two octants per table lookup.
 // ~110 instructions per point against ~400 of the bit-twiddling form, which made curve_key_kernel issue bound (62 % of the
 // issue slots, 0.21 ms at 10 M for a 0.10 ms HBM pass, ncu r02y)
 __device__ __forceinline__ uint64_t hilbert3_lut(uint32_t x, uint32_t y, uint32_t z, int bits, const unsigned char *lut1,
@@ -192,7 +175,7 @@ gather_sorted_kernel(const uint32_t *__restrict__ sidx, int64_t n, const double4
     }
 }
 
-// one warp per entry of table `lvl`; children are points (lvl 0) or entries of table lvl-1
+// one warp per entry of table `lvl` >= 1 (table 0 is built by gather_sorted_kernel); children are entries of table lvl-1
 __global__ void __launch_bounds__(256)
 box_level_kernel(GridDesc g, int lvl, double *__restrict__ box, float4 *__restrict__ boxq)
 {
@@ -202,9 +185,7 @@ box_level_kernel(GridDesc g, int lvl, double *__restrict__ box, float4 *__restri
     const double INF = pos_inf();
     double lo[3] = {INF, INF, INF}, hi[3] = {-INF, -INF, -INF};
     int64_t ch = node * 32 + lane;
-    if (lvl == 0) {
-        if (ch < g.n) { lo[0] = hi[0] = g.sx[ch]; lo[1] = hi[1] = g.sy[ch]; lo[2] = hi[2] = g.sz[ch]; }
-    } else if (ch < g.cnt[lvl - 1]) {
+    if (ch < g.cnt[lvl - 1]) {
         const double *b = box + g.off[lvl - 1];
         int64_t p = g.pitch[lvl - 1];
         lo[0] = b[ch]; lo[1] = b[p + ch]; lo[2] = b[2 * p + ch];

@@ -94,12 +94,14 @@ __device__ __noinline__ void kf_slow_query(const GridDesc &g, int64_t leaf_id, i
         if (lane == 0) out.tier[qpos] = 3;
     }
     if (!out.nx) return;
+    // the reference's summation order (neighbours by increasing (d2, index) = lane order): every lane fetches ITS neighbour once,
+    // the replay broadcasts them in turn (one gather instead of c dependent round trips: a tier-3 query is a single warp's
+    // latency chain, 30 serial loads were a third of it)
+    double vx = 0, vy = 0, vz = 0;
+    if (lane < c) { const double4 r = ld_rec(g.sp4 + st.L.pos[0]); vx = r.x; vy = r.y; vz = r.z; }
     Cumul cu;
     cu.clear();
-    for (int j = 0; j < c; ++j) {
-        int q = __shfl_sync(FULL, st.L.pos[0], j);
-        cu.add(g.sx[q], g.sy[q], g.sz[q]);
-    }
+    for (int j = 0; j < c; ++j) cu.add(shfl_d(vx, j), shfl_d(vy, j), shfl_d(vz, j));
     if (lane == 0) kf_store_normal(cu, g.sidx[leaf_id * 32 + i], out);
     __syncwarp();
 }
