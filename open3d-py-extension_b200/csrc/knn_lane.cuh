@@ -46,7 +46,7 @@ static_assert(K2_LIST % 32 == 0 && K2_LIST <= 256, "the ranks of the hit list li
 #define K2_LUNR 2
 #endif
 #ifndef K2_MINB
-#define K2_MINB 6           // resident blocks per SM the register budget is set for
+#define K2_MINB 7           // resident blocks per SM the register budget is set for
 #endif
 
 struct K2WarpMem {

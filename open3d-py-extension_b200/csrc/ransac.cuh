@@ -105,7 +105,9 @@ __global__ void plane_model_kernel(const double *__restrict__ x, const double *_
 // points within thr + margin take the FP64 evaluation.  7 % of the point x hypothesis pairs of the 10 M scan are inliers, but
 // 38 % of the 32-point warp steps touch one and a thread's four points share the branch: 1.13 ms against 0.97 ms.)
 #define SC_THREADS 256
+#ifndef SC_PPT
 #define SC_PPT 4
+#endif
 #define SC_HB 32   // hypotheses per block (blockIdx.y selects the chunk)
 
 __device__ __forceinline__ double plane_dist(double a, double b, double c, double d, double x, double y, double z)

@@ -111,6 +111,12 @@ def test_sets_forced_paths(kctx, orc):
         kctx.set_option(nat.OPT_KNN_RHO, rho)
         _check_sets(kctx, orc, pts)
     kctx.set_option(nat.OPT_KNN_RHO, 0)
+    # curve keys of 48 bits do not leave room for the index in the key: the (key, index) pair sort instead of the packed one
+    kctx.set_option(nat.OPT_KNN_BITS, 16)
+    try:
+        _check_sets(kctx, orc, pts)
+    finally:
+        kctx.set_option(nat.OPT_KNN_BITS, 0)
 
 
 @pytest.mark.parametrize("mode,radius", [(0, 0.0), (2, 0.5)])

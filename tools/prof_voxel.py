@@ -21,3 +21,6 @@ for k in range(12):
     c.transform(T if k % 2 == 0 else np.linalg.inv(T))
     ts.append(c.timings()[0])
 print('transform ms', ' '.join('%.4f' % t for t in ts[4:]), '-> %.1f GB/s' % (N * 48 / (min(ts[4:]) * 1e-3) / 1e9))
+for k in range(3):
+    plane, inl = c.segment_plane(0.05, 3, 1000, seed=1)[:2]
+    print('segment ms', ' '.join('%.3f' % t for t in c.timings()[:4]), 'inliers', len(inl))
