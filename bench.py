@@ -296,8 +296,10 @@ def run_c2(ctx, nat):
             "transform_ms": t_tr, "normals_ms": t_n, "segment_ms": t_s, "mpoints_per_s": n / ((t_tr + t_n + t_s) * 1e-3) / 1e6}
 
 
-def run_c4(rank, world, local, dist, barrier, frames_total=256, points=131072):
-    """config 4: frames through PointCloudMatProcessors.run_once (reference processors.py:1054-1074), frame f -> rank f mod G"""
+def run_c4(rank, world, local, dist, barrier, frames_total=256, points=131072, per_call=2):
+    """config 4: frames through PointCloudMatProcessors.run_once (reference processors.py:1054-1074), frame f -> rank f mod G;
+    run_once takes a LIST of mats (the reference's generators yield one mat per sensor): per_call frames per call, which the
+    blocks work on side by side (one library context and one host thread per mat)"""
     from open3dpypro import sharding as sh
     from open3dpypro.PointCloudMat import PointCloudMat, ShapeType
     from open3dpypro.processors import Processors, PointCloudMatProcessors
@@ -308,17 +310,21 @@ def run_c4(rank, world, local, dist, barrier, frames_total=256, points=131072):
     frames = {f: lidar_like(points, 2000 + f, np.float32) for f in range(distinct)}
     det = Processors.PlaneDetection(distance_threshold=THR, num_iterations=ITERS, alpha=1.0, seed=7)
     pipes = [Processors.CPUNormals(pinned_outputs=True), det, Processors.PlaneNormalize(detection_uuid=det.uuid, pinned_outputs=True)]
-    mat = PointCloudMat(shape_type=ShapeType.XYZ).build(frames[0])
-    PointCloudMatProcessors.run_once([mat], {}, pipes, validate=True)
+    if len(mine) % per_call:
+        per_call = 1
+    mats = [PointCloudMat(shape_type=ShapeType.XYZ).build(frames[k]) for k in range(per_call)]
+    PointCloudMatProcessors.run_once(mats, {}, pipes, validate=True)
     sec = 0.0
     for rep in range(2):                      # first repetition = warm-up
         barrier(); t0 = time.perf_counter()
-        for f in mine:
-            mat.unsafe_update_mat(frames[f % distinct])
-            PointCloudMatProcessors.run_once([mat], {}, pipes)
+        for j in range(0, len(mine), per_call):
+            for k in range(per_call):
+                mats[k].unsafe_update_mat(frames[mine[j + k] % distinct])
+            PointCloudMatProcessors.run_once(mats, {}, pipes)
         barrier(); sec = time.perf_counter() - t0
     sec = _max_over_ranks([sec], dist, local)[0]
-    return {"workload": f"C4: {frames_total} frames x {points} points through CPUNormals -> PlaneDetection -> PlaneNormalize (run_once), frame f -> rank f mod G, host float32 frames in, host arrays out (page-locked output buffers, two per block)",
+    return {"workload": f"C4: {frames_total} frames x {points} points through CPUNormals -> PlaneDetection -> PlaneNormalize (run_once, {per_call} mats per call), frame f -> rank f mod G, host float32 frames in, host arrays out (page-locked output buffers, two per block and mat)",
+            "mats_per_call": per_call,
             "frames": frames_total, "frames_per_s": frames_total / sec, "mpoints_per_s": frames_total * points / sec / 1e6,
             "ms_per_frame_per_gpu": 1e3 * sec / max(len(mine), 1), "collectives_on_data_path": 0}
 

@@ -476,11 +476,16 @@ def context_lock(device=0):
     return lk
 
 
-def context(device=0):
-    """Process-wide shared context per device, re-created after fork (CUDA state does not survive it)."""
-    key = (os.getpid(), int(device))
+def context(device=0, slot=0):
+    """Process-wide shared context per device, re-created after fork (CUDA state does not survive it).
+    slot > 0: further contexts on the same device (the blocks give every mat of a list its own, so that several mats on one
+    GPU stay resident side by side and can be worked on from several threads; one context = one cloud, one stream)."""
+    key = (os.getpid(), int(device), int(slot))
     ctx = _contexts.get(key)
     if ctx is None:
-        ctx = Context(device)
-        _contexts[key] = ctx
+        with _lock:
+            ctx = _contexts.get(key)
+            if ctx is None:
+                ctx = Context(device)
+                _contexts[key] = ctx
     return ctx

@@ -57,6 +57,18 @@ def _require_array(pcd):
         raise TypeError(f"Expected np.ndarray or torch.Tensor, got {type(pcd.data())}")
 
 
+_MAT_POOL = None
+
+
+def _mat_pool():
+    """threads that work on the mats of one list side by side (library calls release the GIL)"""
+    global _MAT_POOL
+    if _MAT_POOL is None:
+        from concurrent.futures import ThreadPoolExecutor
+        _MAT_POOL = ThreadPoolExecutor(max_workers=4, thread_name_prefix="o3dpp-mat")
+    return _MAT_POOL
+
+
 class _DeviceBlock(PointCloudMatProcessor):
     """common part of the device blocks: one library context per GPU, created lazily in the
     process that runs the block (so blocks survive `run_async`'s JSON round trip and fork).
@@ -68,6 +80,16 @@ class _DeviceBlock(PointCloudMatProcessor):
     multi_gpu: int = -1
     pinned_outputs: bool = False     # outputs land in two alternating page-locked buffers per mat (full-speed D2H); a result
     _pinned: dict = {}               # is then valid until the block has run twice more, like a shm writer's segment
+    parallel_mats: bool = True       # the host mats of one list are worked on side by side, one thread and one library context each
+                                     # (the reference loops over them; the results do not depend on each other)
+
+    def _each(self, pcds, fn, meta=None):
+        """[fn(i, pcd) for i, pcd in enumerate(pcds)], the host mats concurrently when there are several"""
+        if isinstance(meta, dict):
+            meta.setdefault(_RES_KEY, {})                      # created once, before any thread records into it
+        if len(pcds) < 2 or not self.parallel_mats or any(_is_cuda_tensor(p) for p in pcds):
+            return [fn(i, p) for i, p in enumerate(pcds)]
+        return list(_mat_pool().map(lambda ip: fn(*ip), list(enumerate(pcds))))
 
     def _out(self, i, shape, dtype):
         """host array for the output of mat i"""
@@ -92,10 +114,18 @@ class _DeviceBlock(PointCloudMatProcessor):
             return int(pin)
         return i % len(self.num_devices)
 
+    def _slot(self, i):
+        """which of a device's contexts serves mat i: mats that share a GPU get one each"""
+        pin = os.environ.get("O3DPP_DEVICE")
+        if pin is not None and pin != "":
+            return i
+        return i // max(len(self.num_devices), 1)
+
     def _ctx(self, i, pcd=None):
         if _is_cuda_tensor(pcd):
             return nat.context(pcd.device.index)
-        return nat.context(self._device(i))
+        dev = self._device(i)
+        return nat.context(dev, self._slot(i))
 
     def _resident(self, i, pcd, meta, want_handle=False):
         """-> context of mat i whose points are pcd[:, :3] (uploaded unless the previous block left them there);
@@ -149,10 +179,9 @@ class Processors:
             return self.out_mats
 
         def forward_raw(self, pcds_data: List[np.ndarray], pcds_info: List[PointCloudMatInfo] = [], meta={}):
-            res = []
-            for i, pcd in enumerate(pcds_data):
+            def one(i, pcd):
                 if i < len(self.input_shape_types) and self.input_shape_types[i].contains_normals():
-                    continue
+                    return None
                 ctx = self._resident(i, pcd, meta)
                 mode = nat.SEARCH_HYBRID if self.radius > 0 else nat.SEARCH_KNN
                 ctx.drop(nat.ATTR_NORMALS)
@@ -172,8 +201,8 @@ class Processors:
                         out[:, :D] = pcd
                         out[:, D:] = ctx.download(nat.ATTR_NORMALS)
                 self._leave(i, out, ctx, meta, normals_cols=(D == 3))
-                res.append(out)
-            return res
+                return out
+            return [o for o in self._each(pcds_data, one, meta) if o is not None]
 
     class VoxelDownsample(_DeviceBlock):
         title: str = 'voxel_sample'
@@ -183,13 +212,12 @@ class Processors:
             _require_array(pcd)
 
         def forward_raw(self, pcds_data, pcds_info=[], meta={}):
-            res = []
-            for i, pcd in enumerate(pcds_data):
+            def one(i, pcd):
                 ctx = self._resident(i, pcd, meta)
                 V = ctx.voxel(self.voxel_size)
                 rep = ctx.voxel_fetch(V, len(pcd), ["rep"])["rep"]   # rows in ascending voxel key
-                res.append(pcd[torch.as_tensor(rep, device=pcd.device).long()] if _is_cuda_tensor(pcd) else pcd[rep])
-            return res
+                return pcd[torch.as_tensor(rep, device=pcd.device).long()] if _is_cuda_tensor(pcd) else pcd[rep]
+            return self._each(pcds_data, one, meta)
 
     class PlaneDetection(_DeviceBlock):
         title: str = 'plane_detection'
@@ -230,8 +258,7 @@ class Processors:
                 pcds_data = Processors.VoxelDownsample(voxel_size=self.voxel_size, multi_gpu=self.multi_gpu).forward_raw(pcds_data, meta=meta)
             while len(self.best_planes) < len(pcds_data):
                 self.best_planes.append([0., 0., 0., 0.])
-            for i, pcd in enumerate(pcds_data):
-                plane = self.detect(i, pcd, meta)
+            for i, plane in enumerate(self._each(pcds_data, lambda i, pcd: self.detect(i, pcd, meta), meta)):
                 self.best_planes[i] = (np.asarray(self.best_planes[i]) * (1.0 - self.alpha) + plane * self.alpha).tolist()
             self._calls += 1
             meta[self.uuid] = self.best_planes
@@ -274,8 +301,8 @@ class Processors:
         def forward_raw(self, pcds_data, pcds_info=[], meta={}):
             models = meta[self.detection_uuid]
             self.forward_T = [None] * len(pcds_data)
-            res = []
-            for i, pcd in enumerate(pcds_data):
+
+            def one(i, pcd):
                 cuda = _is_cuda_tensor(pcd)
                 dt = np.dtype(str(pcd.dtype).replace("torch.", "")) if cuda else pcd.dtype
                 if dt not in (np.float32, np.float64):
@@ -289,9 +316,8 @@ class Processors:
                     out = self._out(i, pcd.shape, dt)
                     ctx.download_rows6(out)
                     self._leave(i, out, ctx, meta, normals_cols=True)
-                    res.append(out)
                     self.forward_T[i] = T.tolist()
-                    continue
+                    return out
                 ctx.drop(nat.ATTR_NORMALS)
                 ctx.transform(T.astype(np.float64))
                 if cuda:
@@ -309,9 +335,9 @@ class Processors:
                         out[:, :3] = ctx.download_as(nat.ATTR_POINTS, np.empty((len(pcd), 3), dt))
                         out[:, 3:] = pcd[:, 3:]
                 self._leave(i, out, ctx, meta)
-                res.append(out)
                 self.forward_T[i] = T.tolist()
-            return res
+                return out
+            return self._each(pcds_data, one, meta)
 
 
     class RadiusSelection(PointCloudMatProcessor):

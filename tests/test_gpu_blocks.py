@@ -174,6 +174,37 @@ def test_one_upload_per_frame_through_three_blocks(orc, monkeypatch):
     assert np.array_equal(outs[0].data(), b)
 
 
+def test_several_mats_per_call_side_by_side(monkeypatch):
+    """run_once over a LIST of mats (one per sensor in the reference): every mat has its own library context and host thread;
+    the results equal the mats run one at a time, each mat is uploaded once per call, and a second call reuses the contexts"""
+    frames = [lidar_like(30_000 + 1000 * k, 2500 + k, np.float32) for k in range(3)]
+    def pipes_():
+        det = Processors.PlaneDetection(distance_threshold=0.05, num_iterations=100, alpha=1.0, seed=5)
+        return [Processors.CPUNormals(), det, Processors.PlaneNormalize(detection_uuid=det.uuid)], det
+    single = []
+    for f in frames:
+        pipes, det = pipes_()
+        mat = PointCloudMat(shape_type=ShapeType.XYZ).build(f)
+        outs, meta = PointCloudMatProcessors.run_once([mat], {}, pipes, validate=True)
+        single.append((outs[0].data().copy(), list(meta[det.uuid][0])))
+    pipes, det = pipes_()
+    mats = [PointCloudMat(shape_type=ShapeType.XYZ).build(f) for f in frames]
+    uploads = []
+    real = nat.Context.upload
+    monkeypatch.setattr(nat.Context, "upload", lambda self, attr, arr: (uploads.append((id(self), arr.shape)), real(self, attr, arr))[1])
+    outs, meta = PointCloudMatProcessors.run_once(mats, {}, pipes, validate=True)
+    assert sorted(sh for _, sh in uploads) == sorted((len(f), 3) for f in frames)      # one upload per mat
+    assert len({c for c, _ in uploads}) == len(frames)                                  # a context per mat
+    for k in range(len(frames)):
+        assert np.array_equal(outs[k].data(), single[k][0])
+        assert meta[det.uuid][k] == single[k][1]
+    monkeypatch.undo()
+    seq = [Processors.CPUNormals(parallel_mats=False).forward_raw([f], meta={})[0] for f in frames]
+    par = Processors.CPUNormals().forward_raw(frames, meta={})
+    for a, b in zip(seq, par):
+        assert np.array_equal(a, b)
+
+
 def test_cuda_tensor_mats_stay_on_the_device():
     torch = pytest.importorskip("torch")
     frame = lidar_like(30_000, 2400, np.float32)
