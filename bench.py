@@ -296,7 +296,7 @@ def run_c2(ctx, nat):
             "transform_ms": t_tr, "normals_ms": t_n, "segment_ms": t_s, "mpoints_per_s": n / ((t_tr + t_n + t_s) * 1e-3) / 1e6}
 
 
-def run_c4(rank, world, local, dist, barrier, frames_total=256, points=131072, per_call=2):
+def run_c4(rank, world, local, dist, barrier, frames_total=256, points=131072, per_call=4):
     """config 4: frames through PointCloudMatProcessors.run_once (reference processors.py:1054-1074), frame f -> rank f mod G;
     run_once takes a LIST of mats (the reference's generators yield one mat per sensor): per_call frames per call, which the
     blocks work on side by side (one library context and one host thread per mat)"""
