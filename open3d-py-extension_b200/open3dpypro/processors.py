@@ -57,16 +57,17 @@ def _require_array(pcd):
         raise TypeError(f"Expected np.ndarray or torch.Tensor, got {type(pcd.data())}")
 
 
-_MAT_POOL = None
+_MAT_POOL = (None, None)
 
 
 def _mat_pool():
-    """threads that work on the mats of one list side by side (library calls release the GIL)"""
+    """threads that work on the mats of one list side by side (library calls release the GIL); one pool per process:
+    the threads of a parent's pool do not exist in a forked child (run_async)"""
     global _MAT_POOL
-    if _MAT_POOL is None:
+    if _MAT_POOL[0] != os.getpid():
         from concurrent.futures import ThreadPoolExecutor
-        _MAT_POOL = ThreadPoolExecutor(max_workers=4, thread_name_prefix="o3dpp-mat")
-    return _MAT_POOL
+        _MAT_POOL = (os.getpid(), ThreadPoolExecutor(max_workers=4, thread_name_prefix="o3dpp-mat"))
+    return _MAT_POOL[1]
 
 
 class _DeviceBlock(PointCloudMatProcessor):
