@@ -464,6 +464,7 @@ class Context:
 
 _contexts = {}
 _ctx_locks = {}
+_ctx_create_lock = threading.RLock()
 
 
 def context_lock(device=0):
@@ -483,7 +484,8 @@ def context(device=0, slot=0):
     key = (os.getpid(), int(device), int(slot))
     ctx = _contexts.get(key)
     if ctx is None:
-        with _lock:
+        lib()                                   # loads the library under _lock: must not happen inside the lock below
+        with _ctx_create_lock:
             ctx = _contexts.get(key)
             if ctx is None:
                 ctx = Context(device)

@@ -289,3 +289,16 @@ def test_hilbert_table_is_what_the_generator_writes():
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     assert mod.main(check_only=True)
+
+
+def test_first_native_call_may_be_the_shared_context():
+    """nat.context() as the very first call into the library (what __graft_entry__.smoke() does): loading the library takes the
+    module lock, so context() must not hold it while it constructs.  Fresh interpreter, bounded: a deadlock fails the test
+    instead of hanging the suite.  Without a GPU the call raises O3dppError (no CPU fallback)."""
+    import subprocess
+    code = ("import sys; sys.path.insert(0, %r); from open3dpypro import _native as nat\n"
+            "try:\n    c = nat.context(0); print('context', c.size())\n"
+            "except nat.O3dppError as e:\n    print('raised', e.code)\n") % os.path.join(ROOT, "open3d-py-extension_b200")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-500:]
+    assert r.stdout.startswith(("raised", "context")), r.stdout
