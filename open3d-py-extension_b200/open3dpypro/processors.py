@@ -116,15 +116,17 @@ class _DeviceBlock(PointCloudMatProcessor):
         return i % len(self.num_devices)
 
     def _slot(self, i):
-        """which of a device's contexts serves mat i: mats that share a GPU get one each"""
+        """which of a device's contexts serves mat i: mats that share a GPU get one each.  Slot 0 is the context the
+        PointCloud / DeviceCloud API shares under its per-device lock; the blocks, which may run from several threads,
+        stay off it"""
         pin = os.environ.get("O3DPP_DEVICE")
         if pin is not None and pin != "":
-            return i
-        return i // max(len(self.num_devices), 1)
+            return 1 + i
+        return 1 + i // max(len(self.num_devices), 1)
 
     def _ctx(self, i, pcd=None):
         if _is_cuda_tensor(pcd):
-            return nat.context(pcd.device.index)
+            return nat.context(pcd.device.index, 1 + i)
         dev = self._device(i)
         return nat.context(dev, self._slot(i))
 
