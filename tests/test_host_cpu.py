@@ -266,6 +266,106 @@ def _gloo_worker(rank, world, port, q):
         dist.destroy_process_group()
 
 
+class _OracleCtx:
+    """stand-in for nat.Context in the CPU tests of sharding.slab_estimate_normals: the oracle answers what the device would
+    (test infrastructure only).  Honours O3DPP_OPT_QUERY_FIRST the way the library does: only the first m points are answered."""
+
+    def __init__(self):
+        self.pts = np.empty((0, 3))
+        self.nrm = None
+        self.kth = None
+        self.query_first = 0
+        self.calls = []
+
+    def upload(self, attr, arr):
+        self.pts = np.ascontiguousarray(arr, np.float64).reshape(-1, 3)
+        self.nrm = None
+
+    def drop(self, attr):
+        self.nrm = None
+
+    def size(self):
+        return len(self.pts)
+
+    def set_option(self, opt, value):
+        from open3dpypro import _native as nat
+        assert opt == nat.OPT_QUERY_FIRST
+        self.query_first = int(value)
+
+    def estimate_normals(self, mode, knn, radius):
+        from oracle import orc
+        n = len(self.pts)
+        m = self.query_first if 0 < self.query_first < n else n
+        self.calls.append((n, m))
+        full = orc.estimate_normals(self.pts, "knn" if mode == 0 else "hybrid", knn, radius)
+        self.nrm = np.full((n, 3), np.nan)
+        self.nrm[:m] = full[:m]                                  # the others are not queried
+        idx, d2, cnt = orc.knn(self.pts, knn, mode=mode, radius=radius)
+        kth = np.where(cnt >= knn, d2[:, knn - 1], np.inf)
+        self.kth = np.nextafter(kth.astype(np.float32), np.float32(np.inf))     # an upper bound, as the device publishes
+
+    def kth_bound(self):
+        return self.kth
+
+    def download(self, attr, out):
+        out[...] = self.nrm
+        return out
+
+
+def _gloo_knn_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "open3d-py-extension_b200"))
+    import torch.distributed as dist
+    from open3dpypro import sharding as sh, _native as nat
+    from open3dpypro.synthetic import lidar_like
+    from oracle import orc
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    try:
+        pts = lidar_like(6000, 91)
+        part = pts[rank::world]
+        axis, cuts = sh.slab_cuts(part, world, 0.1)
+        owned = sh.redistribute(part, axis, cuts, rank, world)
+        ctx = _OracleCtx()
+        nrm, info = sh.slab_estimate_normals(ctx, owned, axis, cuts, rank, world, nat.SEARCH_KNN, 30)
+        # the second pass queried only the unsafe points, placed first, among the strips + halo
+        assert info["passes"] == 2 and info["halo_points"] > 0
+        n_second, m_second = ctx.calls[1]
+        assert m_second == info["second_pass_queries"] < n_second == info["second_pass_points"]
+        assert ctx.query_first == 0 and len(ctx.pts) == len(owned)          # option reset, owned points left in the context
+        # every owned point got the normal of the whole-scan call (same neighbour sets; direction up to rounding)
+        whole = orc.estimate_normals(pts, "knn", 30)
+        from scipy.spatial import cKDTree
+        dist0, where = cKDTree(pts).query(owned)                            # the scan row of every owned point
+        assert dist0.max() == 0.0
+        cosang = np.abs(np.einsum("ij,ij->i", nrm, whole[where]))
+        assert not np.isnan(nrm).any()
+        assert cosang.min() > 1 - 1e-9, float(cosang.min())
+        q.put((rank, "ok", (len(owned), m_second, n_second)))
+    except Exception:   # noqa: BLE001
+        import traceback
+        q.put((rank, "fail: " + traceback.format_exc(), None))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gloo_world2_pure_knn_slabs_two_passes():
+    """sharding.slab_estimate_normals, pure KNN, world 2 over gloo with the oracle standing in for the device: first pass over
+    the owned points, bound all-reduce, halo exchange, second pass that queries only the unsafe points (O3DPP_OPT_QUERY_FIRST),
+    result equal to the whole-scan normals"""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gloo_knn_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=300) for _ in procs], key=lambda r: r[0])
+    for p in procs:
+        p.join(60)
+    assert all(r[1] == "ok" for r in res), [r[1] for r in res]
+    assert sum(r[2][0] for r in res) == 6000
+
+
 def test_gloo_world2_frames_and_slabs():
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
