@@ -340,6 +340,12 @@ def _gloo_knn_worker(rank, world, port, q):
         cosang = np.abs(np.einsum("ij,ij->i", nrm, whole[where]))
         assert not np.isnan(nrm).any()
         assert cosang.min() > 1 - 1e-9, float(cosang.min())
+        # hybrid search: one halo exchange of width r, one pass, exact
+        ctx2 = _OracleCtx()
+        nrm2, info2 = sh.slab_estimate_normals(ctx2, owned, axis, cuts, rank, world, nat.SEARCH_HYBRID, 30, 0.5)
+        assert info2["passes"] == 1 and info2["halo_width"] == 0.5 and len(ctx2.calls) == 1
+        whole2 = orc.estimate_normals(pts, "hybrid", 30, 0.5)
+        assert np.abs(np.einsum("ij,ij->i", nrm2, whole2[where])).min() > 1 - 1e-9
         q.put((rank, "ok", (len(owned), m_second, n_second)))
     except Exception:   # noqa: BLE001
         import traceback
